@@ -1,0 +1,139 @@
+// common.cuh — shared device-side definitions of the librectify hot path on B200 (sm_100a).
+//
+// Every constant below is carried over from the reference's compile-time configuration
+// (reference src/config.h:10-59, src/line_pencil.h:21, src/line_detector.cpp:203) so that the kernels make the same
+// decisions as the CPU library.  All translation units that include this header are compiled with -fmad=false:
+// the parity contract is bit-exact float32 arithmetic in the order the reference evaluates it, so a multiply and
+// the add that follows it must round separately.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace lrb {
+
+// ---- reference configuration (src/config.h) ---------------------------------------------------------------------
+constexpr float kEps              = 1e-6f;    // config.h:10
+constexpr int   kMaxModels        = 4;        // config.h:23
+constexpr int   kRansacIter       = 10000;    // config.h:29
+constexpr float kLineMaxErr       = 2.0f;     // config.h:50
+constexpr float kLineMinLength    = 5.0f;     // config.h:56
+constexpr int   kComponentMinSize = 5;        // config.h:59
+constexpr float kDegeneracyTol    = 0.05f;    // line_pencil.h:21
+// derived float constants, evaluated as the reference evaluates them (values pinned by tests/golden/kat.npz)
+constexpr float kSeedFactor = 0x1.9999ap-5f;  // 1 - 0.95f            (line_detector.cpp:209, config.h:44)
+constexpr float kTraceKeep  = 0.75f;          // 1 - 0.25f            (filter.cpp:121, config.h:47)
+constexpr float kTolInlier  = 0x1.3f6p-11f;   // 1 - cos(2 deg)       (line_pencil.cpp:143-146, config.h:25)
+constexpr float kTolGarbage = 0x1.3f48p-9f;   // 1 - cos(4 deg)       (config.h:27)
+
+// 5x5 Gaussian-derivative taps, sigma = 1 (reference src/filter.cpp:65-78).  Hx(a,b) = sign(b-2) * kTap[min(a,4-a)][min(b,4-b)],
+// Hy = Hx^T; the centre column (row) is exactly zero.
+#define LRB_K00 0x1.7e13fep-8f
+#define LRB_K01 0x1.ac16bap-7f
+#define LRB_K10 0x1.ac16bap-6f
+#define LRB_K11 0x1.dfa3e4p-5f
+#define LRB_K20 0x1.60e648p-5f
+#define LRB_K21 0x1.8b6582p-4f
+
+// orientation tables sin/cos(float(i*pi)/8) (reference src/line_detector.cpp:142-146)
+static __device__ __constant__ const float kSin[8] = {0.0f, 0x1.87de2cp-2f, 0x1.6a09e6p-1f, 0x1.d906bcp-1f,
+                                               1.0f, 0x1.d906bep-1f, 0x1.6a09e6p-1f, 0x1.87de2ep-2f};
+static __device__ __constant__ const float kCos[8] = {1.0f, 0x1.d906bcp-1f, 0x1.6a09e6p-1f, 0x1.87de2ap-2f,
+                                               -0x1.777a5cp-25f, -0x1.87de28p-2f, -0x1.6a09e6p-1f, -0x1.d906bcp-1f};
+
+// |dx*sin_b + dy*cos_b| exactly as gradient_directions evaluates it (two rounded products, one rounded sum)
+__device__ __forceinline__ float orient_energy(float dx, float dy, int b)
+{
+    return fabsf(__fadd_rn(__fmul_rn(dx, kSin[b]), __fmul_rn(dy, kCos[b])));
+}
+
+// ---- seed ordering ------------------------------------------------------------------------------------------------
+constexpr int kSeedBuckets = 4096;
+
+// ---- per-frame control block (device memory, one per slot; zeroed by k_frame_init) -------------------------------
+constexpr int kMaxRounds = 96;
+struct FrameCtrl {
+    unsigned gmax_bits;        // max gradient magnitude (float bits, mag >= 0 so uint order == float order)
+    int n_seeds;               // peaks emitted by the NMS kernel
+    int seed_overflow;         // more peaks than capacity
+    int flood_overflow;        // a flood ran out of queue / lost-list space in the speculative rounds
+    int n_comp;                // kept components (size > kComponentMinSize)
+    int n_px;                  // pixels in kept components
+    int comp_overflow;
+    int n_lines;               // filtered segments
+    int line_overflow;
+    int rounds_run;
+    int flood_done;            // set by the serial fallback
+    int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
+    // grouping state
+    int num_obs;               // reference estimator.h:119
+    int n_solves;
+    int n_obs[kMaxModels];
+    int winner[kMaxModels];
+    unsigned long long best[kMaxModels];   // (score bits << 32) | ~draw index
+    float best_h[kMaxModels][3];
+    float refined[kMaxModels][3];
+    unsigned long long stream_pos;         // position in the shared uniform stream (carried across solves)
+    int stream_overflow;
+    float bbox[4], cx, cy, scale;
+    int pad_[8];
+};
+
+// ---- views passed to kernels by value -----------------------------------------------------------------------------
+struct Planes {                 // one frame slot = one set of planes; slot s lives at base + s * stride
+    int w, h, pitch;            // pitch in elements, multiple of 16 (TMA needs 16-byte row strides, also for the byte planes)
+    size_t stride;              // elements per slot plane (pitch * h rounded up)
+    const float * img;          // input frames (may alias user memory): img + s * img_stride + r * img_pitch + c
+    size_t img_stride; int img_pitch;
+    float * dx; float * dy; float * mag;
+    uint8_t * bin; uint8_t * mask8;
+    unsigned * owner;
+};
+
+struct Seeds {                  // per slot: s * cap
+    int cap;
+    unsigned * us_mag; unsigned * us_idx;     // unsorted (emission order)
+    unsigned * b_mag;  unsigned * b_idx;      // bucketed
+    unsigned * idx;                           // sorted by (mag desc, raster idx asc): rank -> pixel
+    float * thr;                              // 0.75f * G_bin(seed)
+    uint8_t * bin;
+    unsigned * status;                        // 0 live, 1 dropped, else commit key
+    unsigned * fail_epoch;
+    int * size;
+    int * hist; int * start; int * cursor;    // kSeedBuckets each per slot
+};
+
+struct Comps {                  // per slot
+    int cap; int cap_px;
+    int * rank;                 // kept component -> seed rank
+    int * off;                  // offset into px lists
+    int * size;
+    unsigned * px;              // pixel raster indices in the reference's BFS order
+    float * val;                // G_bin at those pixels
+    float * seg;                // raw LineSegment records (7 x 4 bytes each)
+};
+
+struct Lines {                  // per slot: filtered segments and the pencil model built on them
+    int cap;
+    float * seg;                // LineSegment records (7 x 4 bytes), group_id filled in by k_finalize
+    float * h;                  // 3 per line: unit homogeneous line through the normalised endpoints
+    float * anchor;             // 2 per line: midpoint
+    float * dir;                // 2 per line: unit direction
+    float * len;
+    int * inlier; int * garbage;
+    int * obs;                  // current observation list (indices into the lines)
+    int * tmp;                  // inlier list of the winning hypothesis
+    int * pairs;                // 2 x T per slot: sampled positions in the observation list
+    float * scores;             // kMaxModels x T per slot (-1 = rejected by sample_check); kept for the parity tests
+};
+
+constexpr unsigned kStatusLive = 0u, kStatusDropped = 1u;
+constexpr unsigned kOwnerInit = 0xFFFFFFFFu;          // epoch field 0xFF: never visited, loses every atomicMin
+__device__ __forceinline__ unsigned owner_epoch(unsigned o) { return o >> 24; }
+__device__ __forceinline__ unsigned owner_rank(unsigned o)  { return o & 0x00FFFFFFu; }
+
+struct SegRec { float x1, y1, x2, y2, weight, err; int group_id; };
+
+// warp helpers
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+} // namespace lrb

@@ -1,0 +1,181 @@
+// k1_grad.cu — K1 `grad5x5_bin`: fused image gradients, magnitude, orientation bin and frame maximum.
+//
+// Replaces, for one frame per blockIdx.z:
+//   conv_2d x2 + image_gradients          reference src/filter.cpp:81-98, src/line_detector.cpp:41-49
+//   first two loops of gradient_directions reference src/line_detector.cpp:140-156
+//   max(mag) of find_line_segments        reference src/line_detector.cpp:209
+//
+// Arithmetic contract (bit-exact against the reference compiled without FMA contraction / vectorisation):
+//   dx(r,c) = sum over the 5x5 window in row-major tap order of img*Hx, each product and each sum rounded separately;
+//   the window is a direct 25-tap correlation (NOT separable: separable evaluation rounds differently).
+//   The taps satisfy Hx(a,b) = -Hx(a,4-b) = Hx(4-a,b), Hx(a,2) = 0 and Hy = Hx^T exactly, so only six distinct
+//   magnitudes exist.  Each input pixel is multiplied once by those six magnitudes and the rounded products are
+//   shared by every output and by both filters (IEEE multiplication is sign-symmetric, so x*(-k) == -(x*k)).
+//   Zero taps contribute x*0 = +-0, which can only change the sign of an exactly-zero sum when the input holds
+//   negative zeros; they are skipped ("K1 exactness").
+//
+// Data movement: a (128+4) x (8*RPT+4) halo tile is staged into shared memory by ONE cp.async.bulk.tensor (TMA) per
+// CTA; the copy engine zero-fills outside the image.  Each thread owns a 4-column x RPT-row strip, slides down the
+// tile keeping five partially accumulated output rows in registers, and writes dx/dy/mag as 128-bit and bin as
+// 32-bit coalesced stores.  HBM traffic is the compulsory 4 B read + 13 B written per pixel.
+#include "common.cuh"
+#include "tma.cuh"
+#include "kernels.h"
+
+namespace lrb {
+
+namespace {
+
+constexpr int K1_TW = 128;          // tile width  (32 lanes x 4 columns)
+constexpr int K1_SW = K1_TW + 4;    // staged width incl. 2-px halo (528 B rows: multiple of 16 B as TMA requires)
+
+__device__ __forceinline__ void finish_pixel(float dx, float dy, bool valid, float & odx, float & ody, float & omag, unsigned & obin)
+{
+    dx = valid ? dx : 0.0f;
+    dy = valid ? dy : 0.0f;
+    odx = dx; ody = dy;
+    omag = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));      // line_detector.cpp:47
+    // eight orientation energies |dx*sin(t_i) + dy*cos(t_i)|, t_i = float(i*pi)/8 (line_detector.cpp:142-146).
+    // sin/cos pairs share magnitudes: c2 = s2, c6 = -s2, c7 = -c1, s0 = 0, c0 = 1, s4 = 1.
+    const float S1 = 0x1.87de2cp-2f, C1 = 0x1.d906bcp-1f, S2 = 0x1.6a09e6p-1f, S3 = 0x1.d906bcp-1f, C3 = 0x1.87de2ap-2f;
+    const float C4 = -0x1.777a5cp-25f, S5 = 0x1.d906bep-1f, C5 = -0x1.87de28p-2f, S7 = 0x1.87de2ep-2f;
+    const float dxs2 = __fmul_rn(dx, S2), dys2 = __fmul_rn(dy, S2), dyc1 = __fmul_rn(dy, C1);
+    float g[8];
+    g[0] = fabsf(dy);                                                        // dx*0 + dy*1
+    g[1] = fabsf(__fadd_rn(__fmul_rn(dx, S1), dyc1));
+    g[2] = fabsf(__fadd_rn(dxs2, dys2));
+    g[3] = fabsf(__fadd_rn(__fmul_rn(dx, S3), __fmul_rn(dy, C3)));
+    g[4] = fabsf(__fadd_rn(dx, __fmul_rn(dy, C4)));                          // dx*1 + dy*c4
+    g[5] = fabsf(__fadd_rn(__fmul_rn(dx, S5), __fmul_rn(dy, C5)));
+    g[6] = fabsf(__fsub_rn(dxs2, dys2));                                     // dy*(-s2) == -(dy*s2)
+    g[7] = fabsf(__fsub_rn(__fmul_rn(dx, S7), dyc1));                        // dy*(-c1) == -(dy*c1)
+    // first strict maximum with the running maximum initialised to 0 (line_detector.cpp:152-156)
+    float gm = 0.0f; unsigned b = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { if (g[i] > gm) { b = i; gm = g[i]; } }
+    obin = b;
+}
+
+template <int RPT>
+__global__ void __launch_bounds__(256)
+k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ctrl)
+{
+    constexpr int TH = 8 * RPT, SH = TH + 4;
+    __shared__ __align__(128) float tile[SH * K1_SW];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ unsigned wmax[8];
+
+    const int slot = blockIdx.z;
+    const int x0 = blockIdx.x * K1_TW, y0 = blockIdx.y * TH;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(&bar, SH * K1_SW * sizeof(float));
+        tma_load_3d(tile, &tmap, x0 - 2, y0 - 2, slot, &bar);
+    }
+    mbar_wait(&bar, 0);
+
+    const int ty0 = warp * RPT;                 // first output row of this thread inside the tile
+    const int xq = x0 + lane * 4;               // first output column
+    float ax[RPT][4], ay[RPT][4];
+    float tmax = 0.0f;
+
+    float * pdx = P.dx + slot * P.stride; float * pdy = P.dy + slot * P.stride; float * pmag = P.mag + slot * P.stride;
+    uint8_t * pbin = P.bin + slot * P.stride;
+
+#pragma unroll
+    for (int i = 0; i < RPT + 4; ++i) {
+        const float4 lo = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4]);
+        const float4 hi = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4 + 4]);
+        const float p[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+        float m[3][2][8];                       // m[a'][b'][j] = p[j] * |Hx(a',b')|
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            m[0][0][j] = __fmul_rn(p[j], LRB_K00); m[0][1][j] = __fmul_rn(p[j], LRB_K01);
+            m[1][0][j] = __fmul_rn(p[j], LRB_K10); m[1][1][j] = __fmul_rn(p[j], LRB_K11);
+            m[2][0][j] = __fmul_rn(p[j], LRB_K20); m[2][1][j] = __fmul_rn(p[j], LRB_K21);
+        }
+#pragma unroll
+        for (int j = 0; j < RPT; ++j) {
+            const int a = i - j;                // tap row of input row i for output row j
+            if (a < 0 || a > 4) continue;
+            const int ar = a < 2 ? a : 4 - a;   // 0,1,2,1,0
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                // Hx row a: -K[ar][0], -K[ar][1], 0, +K[ar][1], +K[ar][0]
+                float sx = (a == 0) ? -m[ar][0][c] : __fsub_rn(ax[j][c], m[ar][0][c]);
+                sx = __fsub_rn(sx, m[ar][1][c + 1]);
+                sx = __fadd_rn(sx, m[ar][1][c + 3]);
+                sx = __fadd_rn(sx, m[ar][0][c + 4]);
+                ax[j][c] = sx;
+                // Hy row a: sign(a-2) * { K[0][ar], K[1][ar], K[2][ar], K[1][ar], K[0][ar] }, zero for a == 2
+                if (a != 2) {
+                    const int ac = ar;          // 0 or 1 here
+                    float sy;
+                    if (a < 2) {
+                        sy = (a == 0) ? -m[0][ac][c] : __fsub_rn(ay[j][c], m[0][ac][c]);
+                        sy = __fsub_rn(sy, m[1][ac][c + 1]);
+                        sy = __fsub_rn(sy, m[2][ac][c + 2]);
+                        sy = __fsub_rn(sy, m[1][ac][c + 3]);
+                        sy = __fsub_rn(sy, m[0][ac][c + 4]);
+                    } else {
+                        sy = __fadd_rn(ay[j][c], m[0][ac][c]);
+                        sy = __fadd_rn(sy, m[1][ac][c + 1]);
+                        sy = __fadd_rn(sy, m[2][ac][c + 2]);
+                        sy = __fadd_rn(sy, m[1][ac][c + 3]);
+                        sy = __fadd_rn(sy, m[0][ac][c + 4]);
+                    }
+                    ay[j][c] = sy;
+                }
+            }
+        }
+        // output row j = i - 4 is complete
+        if (i >= 4) {
+            const int j = i - 4;
+            const int y = y0 + ty0 + j;
+            if (y < P.h && xq < P.pitch) {
+                const bool vy = (y >= 2) && (y < P.h - 2);
+                float4 odx, ody, omag; unsigned b0, b1, b2, b3;
+                finish_pixel(ax[j][0], ay[j][0], vy && (xq + 0 >= 2) && (xq + 0 < P.w - 2), odx.x, ody.x, omag.x, b0);
+                finish_pixel(ax[j][1], ay[j][1], vy && (xq + 1 >= 2) && (xq + 1 < P.w - 2), odx.y, ody.y, omag.y, b1);
+                finish_pixel(ax[j][2], ay[j][2], vy && (xq + 2 >= 2) && (xq + 2 < P.w - 2), odx.z, ody.z, omag.z, b2);
+                finish_pixel(ax[j][3], ay[j][3], vy && (xq + 3 >= 2) && (xq + 3 < P.w - 2), odx.w, ody.w, omag.w, b3);
+                const size_t o = (size_t)y * P.pitch + xq;
+                *reinterpret_cast<float4 *>(pdx + o) = odx;
+                *reinterpret_cast<float4 *>(pdy + o) = ody;
+                *reinterpret_cast<float4 *>(pmag + o) = omag;
+                *reinterpret_cast<unsigned *>(pbin + o) = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+                tmax = fmaxf(tmax, fmaxf(fmaxf(omag.x, omag.y), fmaxf(omag.z, omag.w)));
+            }
+        }
+    }
+
+    // frame maximum of mag: mag >= 0, so the uint order of the bit patterns is the float order
+    unsigned um = __float_as_uint(tmax);
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) um = max(um, __shfl_xor_sync(0xffffffffu, um, s));
+    if (lane == 0) wmax[warp] = um;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned v = wmax[0];
+#pragma unroll
+        for (int k = 1; k < 8; ++k) v = max(v, wmax[k]);
+        if (v) atomicMax(&ctrl[slot].gmax_bits, v);
+    }
+}
+
+} // namespace
+
+void launch_grad(const CUtensorMap & tmap, const Planes & P, FrameCtrl * ctrl, int n_slots, cudaStream_t st)
+{
+    constexpr int RPT = 8;
+    dim3 grid((P.w + K1_TW - 1) / K1_TW, (P.h + 8 * RPT - 1) / (8 * RPT), n_slots);
+    k_grad5x5_bin<RPT><<<grid, 256, 0, st>>>(tmap, P, ctrl);
+}
+
+int grad_tile_w() { return K1_SW; }
+int grad_tile_h() { return 8 * 8 + 4; }
+
+} // namespace lrb

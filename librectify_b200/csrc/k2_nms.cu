@@ -1,0 +1,263 @@
+// k2_nms.cu — K2 `nms5x5_seeds` (+ the dilated orientation mask) and K3, the exact seed ordering.
+//
+// Replaces, per frame:
+//   maximum_filter + find_peaks           reference src/filter.cpp:29-43,161-195 (threshold src/line_detector.cpp:209)
+//   binary_dilate of the 8 bin masks      reference src/filter.cpp:46-62, src/line_detector.cpp:163-171
+//   std::sort of the peaks + seed_bin     reference src/filter.cpp:188, src/line_detector.cpp:216-220
+//
+// K2 reads mag (4 B/px) and bin (1 B/px) once, through TMA halo tiles, and writes one byte per pixel:
+//   mask8(p) bit b  <=>  p is not on the 1-px border and some 3x3 neighbour has bin == b
+// which is all that the reference's eight dilated, masked energy planes (66 MB at 1080p) are ever used for:
+//   G_b(p) = mask8(p).b ? |dx(p) sin_b + dy(p) cos_b| : 0.
+// Peaks (mag == 5x5 max, mag > max(mag)*(1-0.95f), 2-px border excluded) are appended to a per-frame list with one
+// warp-aggregated atomic per warp and histogrammed into kSeedBuckets monotone magnitude buckets.
+//
+// K3 turns the unordered list into the reference's processing order — magnitude descending, raster index ascending
+// inside exact ties (std::sort is unstable there; the tests accept any order inside a tie group) — without a general
+// sort: bucket scan -> scatter -> exact rank inside the (tiny) bucket by counting.  The rank is the seed's flood
+// priority and its slot in every per-seed array.
+#include "common.cuh"
+#include "tma.cuh"
+#include "kernels.h"
+
+namespace lrb {
+
+namespace {
+
+constexpr int K2_TW = 128, K2_TH = 32;
+constexpr int K2_MW = K2_TW + 4, K2_MH = K2_TH + 4;        // mag tile, 2-px halo
+constexpr int K2_BW = 144, K2_BH = K2_TH + 2;              // bin tile, 1-px halo (130 B needed; 144 = next multiple of 16)
+
+// monotone (non-decreasing in mag) bucket index, then flipped so that bucket 0 holds the largest magnitudes
+__device__ __forceinline__ int seed_bucket(float mag, float thr, float gmax)
+{
+    const float scale = __fdiv_rn((float)kSeedBuckets, __fsub_rn(gmax, thr));
+    int b = (int)__fmul_rn(__fsub_rn(mag, thr), scale);
+    b = min(max(b, 0), kSeedBuckets - 1);
+    return kSeedBuckets - 1 - b;
+}
+
+__global__ void __launch_bounds__(256)
+k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
+               Planes P, Seeds S, FrameCtrl * ctrl)
+{
+    __shared__ __align__(128) float tmag[K2_MH * K2_MW];
+    __shared__ __align__(128) uint8_t tbin[K2_BH * K2_BW];
+    __shared__ __align__(8) uint64_t bar;
+
+    const int slot = blockIdx.z;
+    const int x0 = blockIdx.x * K2_TW, y0 = blockIdx.y * K2_TH;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(&bar, K2_MH * K2_MW * 4 + K2_BH * K2_BW);
+        tma_load_3d(tmag, &tmap_mag, x0 - 2, y0 - 2, slot, &bar);
+        tma_load_3d(tbin, &tmap_bin, x0 - 1, y0 - 1, slot, &bar);
+    }
+    const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
+    const float thr = __fmul_rn(gmax, kSeedFactor);
+    mbar_wait(&bar, 0);
+
+    const int ty0 = warp * 4;                   // 4 output rows per thread
+    const int xq = x0 + lane * 4;               // 4 output columns per thread
+
+    // ---- 5x5 maximum, separable (max is exact and order-free) ----------------------------------------------------
+    float hm[8][4], ctr[4][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float4 lo = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4]);
+        const float4 hi = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4 + 4]);
+        const float p[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            hm[i][c] = fmaxf(fmaxf(fmaxf(p[c], p[c + 1]), fmaxf(p[c + 2], p[c + 3])), p[c + 4]);
+            if (i >= 2 && i < 6) ctr[i - 2][c] = p[c + 2];
+        }
+    }
+    unsigned peakmask = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int y = y0 + ty0 + j;
+        const bool vy = (y >= 2) && (y < P.h - 2);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float mx = fmaxf(fmaxf(fmaxf(hm[j][c], hm[j + 1][c]), fmaxf(hm[j + 2][c], hm[j + 3][c])), hm[j + 4][c]);
+            const int x = xq + c;
+            const bool v = vy && (x >= 2) && (x < P.w - 2);
+            if (v && ctr[j][c] == mx && ctr[j][c] > thr) peakmask |= 1u << (j * 4 + c);
+        }
+    }
+
+    // ---- 3x3 dilation of the one-hot bin masks ---------------------------------------------------------------------
+    // tbin row i <-> image row y0-1+i, byte k <-> image column x0-1+k; this thread needs columns xq-1 .. xq+4
+    unsigned hor[6];                            // per staged row: 4 bytes, byte c = OR of one-hot(bin) over columns c-1..c+1
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const unsigned w0 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4]);
+        const unsigned w1 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 4]);
+        unsigned oh[6];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) oh[k] = 1u << ((w0 >> (8 * k)) & 7u);
+        oh[4] = 1u << (w1 & 7u); oh[5] = 1u << ((w1 >> 8) & 7u);
+        // out-of-image staged bytes are 0 (bin 0); they are only ever combined into border pixels, which are forced to 0
+        hor[i] = (oh[0] | oh[1] | oh[2]) | ((oh[1] | oh[2] | oh[3]) << 8) | ((oh[2] | oh[3] | oh[4]) << 16) | ((oh[3] | oh[4] | oh[5]) << 24);
+    }
+    uint8_t * pmask = P.mask8 + slot * P.stride;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int y = y0 + ty0 + j;
+        if (y < P.h && xq < P.pitch) {
+            unsigned mword = hor[j] | hor[j + 1] | hor[j + 2];
+            const bool vy = (y >= 1) && (y < P.h - 1);
+            unsigned keep = 0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { const int x = xq + c; if (vy && x >= 1 && x < P.w - 1) keep |= 0xFFu << (8 * c); }
+            *reinterpret_cast<unsigned *>(pmask + (size_t)y * P.pitch + xq) = mword & keep;
+        }
+    }
+
+    // ---- append peaks: one atomic per warp --------------------------------------------------------------------------
+    const int cnt = __popc(peakmask);
+    int incl = cnt;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += t; }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&ctrl[slot].n_seeds, total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    int o = base + incl - cnt;
+    unsigned * us_mag = S.us_mag + (size_t)slot * S.cap; unsigned * us_idx = S.us_idx + (size_t)slot * S.cap;
+    int * hist = S.hist + (size_t)slot * kSeedBuckets;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (peakmask & (1u << (j * 4 + c))) {
+                if (o < S.cap) {
+                    us_mag[o] = __float_as_uint(ctr[j][c]);
+                    us_idx[o] = (unsigned)((y0 + ty0 + j) * P.w + (xq + c));      // raster index in the dense W x H image
+                    atomicAdd(&hist[seed_bucket(ctr[j][c], thr, gmax)], 1);
+                } else {
+                    ctrl[slot].seed_overflow = 1;
+                }
+                ++o;
+            }
+}
+
+// exclusive scan of the bucket histogram; one block of 1024 threads per frame, 4 buckets per thread
+__global__ void __launch_bounds__(1024) k_seed_scan(Seeds S, FrameCtrl * ctrl)
+{
+    static_assert(kSeedBuckets == 4096, "4 buckets per thread");
+    __shared__ int wsum[32];
+    const int slot = blockIdx.x;
+    int * hist = S.hist + (size_t)slot * kSeedBuckets; int * start = S.start + (size_t)slot * kSeedBuckets;
+    int * cursor = S.cursor + (size_t)slot * kSeedBuckets;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int4 h = *reinterpret_cast<const int4 *>(hist + 4 * t);
+    const int mine = h.x + h.y + h.z + h.w;
+    int incl = mine;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += v; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int v = wsum[lane];
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, s); if (lane >= s) v += u; }
+        wsum[lane] = v;
+    }
+    __syncthreads();
+    const int ex = incl - mine + (warp ? wsum[warp - 1] : 0);
+    *reinterpret_cast<int4 *>(start + 4 * t) = make_int4(ex, ex + h.x, ex + h.x + h.y, ex + h.x + h.y + h.z);
+    *reinterpret_cast<int4 *>(cursor + 4 * t) = make_int4(0, 0, 0, 0);
+    if (t == 0) {
+        if (ctrl[slot].n_seeds > S.cap) { ctrl[slot].n_seeds = S.cap; ctrl[slot].seed_overflow = 1; }
+        ctrl[slot].live[0] = ctrl[slot].n_seeds;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_seed_scatter(Seeds S, FrameCtrl * ctrl)
+{
+    const int slot = blockIdx.y;
+    const int n = min(ctrl[slot].n_seeds, S.cap);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
+    const float thr = __fmul_rn(gmax, kSeedFactor);
+    const size_t so = (size_t)slot * S.cap, bo = (size_t)slot * kSeedBuckets;
+    const unsigned m = S.us_mag[so + i];
+    const int d = seed_bucket(__uint_as_float(m), thr, gmax);
+    const int pos = S.start[bo + d] + atomicAdd(&S.cursor[bo + d], 1);
+    S.b_mag[so + pos] = m;
+    S.b_idx[so + pos] = S.us_idx[so + i];
+}
+
+// exact rank inside the bucket by counting, then per-seed flood parameters
+__global__ void __launch_bounds__(256) k_seed_rank(Planes P, Seeds S, FrameCtrl * ctrl)
+{
+    const int slot = blockIdx.y;
+    const int n = min(ctrl[slot].n_seeds, S.cap);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
+    const float thr = __fmul_rn(gmax, kSeedFactor);
+    const size_t so = (size_t)slot * S.cap, bo = (size_t)slot * kSeedBuckets;
+    const unsigned m = S.b_mag[so + i], ix = S.b_idx[so + i];
+    const int d = seed_bucket(__uint_as_float(m), thr, gmax);
+    const int lo = S.start[bo + d], hi = lo + S.hist[bo + d];
+    int before = 0;
+    for (int j = lo; j < hi; ++j) {
+        const unsigned mj = S.b_mag[so + j], ij = S.b_idx[so + j];
+        before += (mj > m) || (mj == m && ij < ix);          // positive floats: bit order == value order
+    }
+    const int rank = lo + before;
+    const int r = ix / P.w, c = ix - r * P.w;
+    const size_t po = (size_t)slot * P.stride + (size_t)r * P.pitch + c;
+    const int b = P.bin[po];
+    S.idx[so + rank] = ix;
+    S.bin[so + rank] = (uint8_t)b;
+    // flood threshold (1 - 0.25f) * G_b(seed)   (reference src/filter.cpp:119-121)
+    S.thr[so + rank] = __fmul_rn(kTraceKeep, orient_energy(P.dx[po], P.dy[po], b));
+    S.status[so + rank] = kStatusLive;
+    S.fail_epoch[so + rank] = 0u;
+    S.size[so + rank] = 0;
+}
+
+// zero the per-frame control block and the bucket histogram
+__global__ void __launch_bounds__(256) k_frame_init(Seeds S, FrameCtrl * ctrl)
+{
+    const int slot = blockIdx.x;
+    int * c = reinterpret_cast<int *>(&ctrl[slot]);
+    for (int i = threadIdx.x; i < (int)(sizeof(FrameCtrl) / sizeof(int)); i += blockDim.x) c[i] = 0;
+    int * hist = S.hist + (size_t)slot * kSeedBuckets;
+    for (int i = threadIdx.x; i < kSeedBuckets; i += blockDim.x) hist[i] = 0;
+}
+
+} // namespace
+
+void launch_frame_init(const Seeds & S, FrameCtrl * ctrl, int n_slots, cudaStream_t st)
+{
+    k_frame_init<<<n_slots, 256, 0, st>>>(S, ctrl);
+}
+
+void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, const Planes & P, const Seeds & S,
+                FrameCtrl * ctrl, int n_slots, cudaStream_t st)
+{
+    dim3 grid((P.w + K2_TW - 1) / K2_TW, (P.h + K2_TH - 1) / K2_TH, n_slots);
+    k_nms5x5_seeds<<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl);
+}
+
+void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st)
+{
+    k_seed_scan<<<n_slots, 1024, 0, st>>>(S, ctrl);
+    dim3 grid((seeds_hint + 255) / 256, n_slots);
+    k_seed_scatter<<<grid, 256, 0, st>>>(S, ctrl);
+    k_seed_rank<<<grid, 256, 0, st>>>(P, S, ctrl);
+}
+
+void nms_tile_dims(int * mw, int * mh, int * bw, int * bh) { *mw = K2_MW; *mh = K2_MH; *bw = K2_BW; *bh = K2_BH; }
+
+} // namespace lrb

@@ -1,0 +1,269 @@
+// k5_fit.cu — component selection, the reference's BFS pixel order, and K5 `fit_segments`.
+//
+// Replaces the tail of find_components (size > 5 filter, reference src/line_detector.cpp:111-119), the pixel order of
+// flood (src/filter.cpp:123-151), fit_lines_to_components (src/line_detector.cpp:66-89) and fit_line_parameters
+// (src/geometry.cpp:20-61).
+//
+// After the speculative rounds each committed seed owns exactly its final region (owner[p] == status[rank]), but the
+// rounds discover pixels in arbitrary order.  The reference's weighted sums run in BFS acceptance order, and float
+// addition is not associative, so one warp per kept component re-walks its region in the reference's order:
+// four accepted pixels x eight neighbours (in the reference's neighbour order) are tested per step, duplicates inside
+// the step resolved to the lowest lane, and accepted pixels appended in lane order — which is exactly the FIFO order
+// of the sequential flood.  The fit then evaluates every sum sequentially in that order (element terms are produced by
+// 32 lanes in parallel, a single lane per running sum adds them up), so raw segments are bit-identical to the CPU code.
+#include "common.cuh"
+#include "eig.cuh"
+#include "kernels.h"
+
+namespace lrb {
+
+namespace {
+
+constexpr int FIT_WARPS = 4;
+
+static __device__ __constant__ const int kDr[8] = {0, 0, 1, -1, -1, -1, 1, 1};
+static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
+
+// kept components in seed order: ordered compaction over ranks; one block per frame
+__global__ void __launch_bounds__(1024) k_comp_select(Seeds S, Comps K, FrameCtrl * ctrl, int rounds_total)
+{
+    __shared__ int wcnt[32], wpx[32];
+    __shared__ int base_c, base_px;
+    const int slot = blockIdx.x;
+    FrameCtrl & C = ctrl[slot];
+    const int n = C.n_seeds;
+    const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    // floods not finished (more rounds or the serial fallback needed): publish nothing; the host re-runs from here
+    if ((C.live[rounds_total] != 0 && !C.flood_done) || C.flood_overflow) {
+        if (t == 0) { C.n_comp = 0; C.n_px = 0; }
+        return;
+    }
+    if (t == 0) { base_c = 0; base_px = 0; }
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += 1024) {
+        const int i = i0 + t;
+        int keep = 0, sz = 0;
+        if (i < n) {
+            const unsigned st = S.status[so + i];
+            sz = S.size[so + i];
+            keep = (st > kStatusDropped) && (sz > kComponentMinSize);          // line_detector.cpp:111
+            if (!keep) sz = 0;
+        }
+        int ic = keep, ip = sz;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const int a = __shfl_up_sync(0xffffffffu, ic, s), b = __shfl_up_sync(0xffffffffu, ip, s);
+            if (lane >= s) { ic += a; ip += b; }
+        }
+        if (lane == 31) { wcnt[warp] = ic; wpx[warp] = ip; }
+        __syncthreads();
+        if (warp == 0) {
+            int a = wcnt[lane], b = wpx[lane];
+#pragma unroll
+            for (int s = 1; s < 32; s <<= 1) {
+                const int x = __shfl_up_sync(0xffffffffu, a, s), y = __shfl_up_sync(0xffffffffu, b, s);
+                if (lane >= s) { a += x; b += y; }
+            }
+            wcnt[lane] = a; wpx[lane] = b;
+        }
+        __syncthreads();
+        const int cpos = base_c + ic - keep + (warp ? wcnt[warp - 1] : 0);
+        const int ppos = base_px + ip - sz + (warp ? wpx[warp - 1] : 0);
+        if (keep) {
+            if (cpos < K.cap && ppos + sz <= K.cap_px) { K.rank[ko + cpos] = i; K.off[ko + cpos] = ppos; K.size[ko + cpos] = sz; }
+            else C.comp_overflow = 1;
+        }
+        __syncthreads();
+        if (t == 0) { base_c += wcnt[31]; base_px += wpx[31]; }
+        __syncthreads();
+    }
+    if (t == 0) { C.n_comp = min(base_c, K.cap); C.n_px = base_px; }
+}
+
+// running sums evaluated strictly in list order: lanes 0..NS-1 each own one sum; terms come through shared memory
+template <int NS>
+__device__ __forceinline__ void seq_accumulate(float (*stage)[32], const float (&term)[NS], int valid, int lane, bool first_chunk, float & acc)
+{
+#pragma unroll
+    for (int s = 0; s < NS; ++s) stage[s][lane] = term[s];
+    __syncwarp();
+    if (lane < NS) {
+        for (int k = 0; k < valid; ++k) {
+            const float t = stage[lane][k];
+            acc = (first_chunk && k == 0) ? t : __fadd_rn(acc, t);
+        }
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(FIT_WARPS * 32)
+k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
+{
+    __shared__ float stage_all[FIT_WARPS][3][32];
+    const int slot = blockIdx.y;
+    FrameCtrl & C = ctrl[slot];
+    const int ncomp = C.n_comp;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float (*stage)[32] = stage_all[warp];
+    const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap, pbase = (size_t)slot * P.stride;
+    unsigned * owner = P.owner + pbase;
+    const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
+
+    for (int comp = blockIdx.x * FIT_WARPS + warp; comp < ncomp; comp += gridDim.x * FIT_WARPS) {
+        const int rank = K.rank[ko + comp];
+        const int n = K.size[ko + comp];
+        unsigned * px = K.px + (size_t)slot * K.cap_px + K.off[ko + comp];
+        float * val = K.val + (size_t)slot * K.cap_px + K.off[ko + comp];
+        const unsigned ckey = S.status[so + rank];
+        const unsigned listed = 0xFF000000u | (unsigned)rank;                  // epoch 0xFF: reads as "never stamped" later
+        const int b = S.bin[so + rank];
+        const unsigned spx = S.idx[so + rank];
+
+        // ---- pixel list in the reference's acceptance order (filter.cpp:123-151) ----------------------------------
+        int head = 0, tail = 1;
+        if (lane == 0) {
+            const int sr = spx / P.w, sc = spx - sr * P.w;
+            __stcg(px, ((unsigned)sr << 16) | (unsigned)sc);
+            __stcg(owner + (size_t)sr * P.pitch + sc, listed);
+        }
+        __syncwarp();
+        while (head < tail) {
+            const int cnt = min(4, tail - head);
+            const int pslot = lane >> 3, k = lane & 7;
+            const bool act = pslot < cnt;
+            const unsigned prc = __ldcg(px + head + (act ? pslot : 0));
+            head += cnt;
+            const int r = (int)(prc >> 16) + kDr[k], c = (int)(prc & 0xFFFFu) + kDc[k];
+            const size_t po = (size_t)r * P.pitch + c;                          // parents are interior pixels: in range
+            const bool member = act && (__ldcg(owner + po) == ckey);
+            const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
+            const unsigned long long mkey = member ? (unsigned long long)rcq : ((1ull << 40) | (unsigned)lane);
+            const unsigned same = __match_any_sync(0xffffffffu, mkey);
+            const bool take = member && (lane == __ffs(same) - 1);
+            const unsigned tm = __ballot_sync(0xffffffffu, take);
+            if (take) {
+                const int pos = tail + __popc(tm & ((1u << lane) - 1));
+                if (pos < n) __stcg(px + pos, rcq);
+                __stcg(owner + po, listed);
+            }
+            tail += __popc(tm);
+            __syncwarp();
+        }
+        // tail == n by construction (the committed flood counted the same set)
+        const int m = min(tail, n);
+
+        // ---- fit_line_parameters (geometry.cpp:20-61); X = (row, col), weights = G_b ------------------------------
+        float acc = 0.f;
+        // pass 1: weights and their sum
+        for (int i0 = 0; i0 < m; i0 += 32) {
+            const int i = i0 + lane; const int valid = min(32, m - i0);
+            float t[1] = {0.f};
+            if (i < m) {
+                const unsigned rc = __ldcg(px + i);
+                const size_t po = (size_t)(rc >> 16) * P.pitch + (rc & 0xFFFFu);
+                t[0] = orient_energy(__ldg(dx + po), __ldg(dy + po), b);
+                val[i] = t[0];
+            }
+            seq_accumulate<1>(stage, t, valid, lane, i0 == 0, acc);
+        }
+        const float wsum = __shfl_sync(0xffffffffu, acc, 0);
+        __syncwarp();
+        // pass 2: weighted mean a = sum X * (w / wsum)
+        acc = 0.f;
+        for (int i0 = 0; i0 < m; i0 += 32) {
+            const int i = i0 + lane; const int valid = min(32, m - i0);
+            float t[2] = {0.f, 0.f};
+            if (i < m) {
+                const unsigned rc = __ldcg(px + i);
+                const float wt = __fdiv_rn(val[i], wsum);
+                t[0] = __fmul_rn((float)(rc >> 16), wt); t[1] = __fmul_rn((float)(rc & 0xFFFFu), wt);
+            }
+            seq_accumulate<2>(stage, t, valid, lane, i0 == 0, acc);
+        }
+        const float a0 = __shfl_sync(0xffffffffu, acc, 0), a1 = __shfl_sync(0xffffffffu, acc, 1);
+        // pass 3: lower triangle of centered^T diag(wt) centered: (c_i * wt) * c_j
+        acc = 0.f;
+        for (int i0 = 0; i0 < m; i0 += 32) {
+            const int i = i0 + lane; const int valid = min(32, m - i0);
+            float t[3] = {0.f, 0.f, 0.f};
+            if (i < m) {
+                const unsigned rc = __ldcg(px + i);
+                const float wt = __fdiv_rn(val[i], wsum);
+                const float c0 = __fsub_rn((float)(rc >> 16), a0), c1 = __fsub_rn((float)(rc & 0xFFFFu), a1);
+                t[0] = __fmul_rn(__fmul_rn(c0, wt), c0);       // cov(0,0)
+                t[1] = __fmul_rn(__fmul_rn(c1, wt), c0);       // cov(1,0)
+                t[2] = __fmul_rn(__fmul_rn(c1, wt), c1);       // cov(1,1)
+            }
+            seq_accumulate<3>(stage, t, valid, lane, i0 == 0, acc);
+        }
+        float cov[4];
+        cov[0] = __shfl_sync(0xffffffffu, acc, 0); cov[2] = __shfl_sync(0xffffffffu, acc, 1); cov[3] = __shfl_sync(0xffffffffu, acc, 2);
+        cov[1] = cov[2];
+        float eval[2], evec[4];
+        sym_eig<2>(cov, eval, evec);                           // every lane computes the same thing
+        const float d0 = evec[2], d1 = evec[3];                // column 1: largest eigenvalue = direction (geometry.cpp:40)
+        const float n0 = evec[0], n1 = evec[1];                // column 0: normal
+        // pass 4: projection range (order-free) and mean |normal residual| (ordered)
+        acc = 0.f;
+        float tmin = INFINITY, tmax = -INFINITY;
+        for (int i0 = 0; i0 < m; i0 += 32) {
+            const int i = i0 + lane; const int valid = min(32, m - i0);
+            float t[1] = {0.f};
+            if (i < m) {
+                const unsigned rc = __ldcg(px + i);
+                const float c0 = __fsub_rn((float)(rc >> 16), a0), c1 = __fsub_rn((float)(rc & 0xFFFFu), a1);
+                const float tt = __fadd_rn(__fmul_rn(c0, d0), __fmul_rn(c1, d1));
+                tmin = fminf(tmin, tt); tmax = fmaxf(tmax, tt);
+                t[0] = fabsf(__fadd_rn(__fmul_rn(c0, n0), __fmul_rn(c1, n1)));
+            }
+            seq_accumulate<1>(stage, t, valid, lane, i0 == 0, acc);
+        }
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) {
+            tmin = fminf(tmin, __shfl_xor_sync(0xffffffffu, tmin, s));
+            tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, s));
+        }
+        if (lane == 0) {
+            SegRec s;
+            s.y1 = __fadd_rn(a0, __fmul_rn(d0, tmin)); s.x1 = __fadd_rn(a1, __fmul_rn(d1, tmin));      // endpoint (row, col) -> (y, x)
+            s.y2 = __fadd_rn(a0, __fmul_rn(d0, tmax)); s.x2 = __fadd_rn(a1, __fmul_rn(d1, tmax));
+            s.weight = __fdiv_rn(wsum, (float)m);
+            s.err = __fdiv_rn(acc, (float)m);
+            s.group_id = -1;
+            reinterpret_cast<SegRec *>(K.seg)[ko + comp] = s;
+        }
+        __syncwarp();
+    }
+}
+
+// debug/test helper: label plane (kept component index, -1 elsewhere) from the pixel lists
+__global__ void k_labels(Planes P, Comps K, FrameCtrl * ctrl, int * labels, int slot)
+{
+    const int ncomp = ctrl[slot].n_comp;
+    const size_t ko = (size_t)slot * K.cap;
+    for (int comp = blockIdx.x; comp < ncomp; comp += gridDim.x) {
+        const unsigned * px = K.px + (size_t)slot * K.cap_px + K.off[ko + comp];
+        const int n = K.size[ko + comp];
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const unsigned rc = px[i];
+            labels[(size_t)(rc >> 16) * P.w + (rc & 0xFFFFu)] = comp;
+        }
+    }
+}
+
+} // namespace
+
+void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int rounds_total, cudaStream_t st)
+{
+    k_comp_select<<<n_slots, 1024, 0, st>>>(S, K, ctrl, rounds_total);
+    dim3 grid(max(1, 148 * 8 / max(1, min(n_slots, 8))), n_slots);
+    k_fit_segments<<<grid, FIT_WARPS * 32, 0, st>>>(P, S, K, ctrl);
+}
+
+void launch_labels(const Planes & P, const Comps & K, FrameCtrl * ctrl, int * labels, int slot, cudaStream_t st)
+{
+    k_labels<<<256, 128, 0, st>>>(P, K, ctrl, labels, slot);
+}
+
+} // namespace lrb

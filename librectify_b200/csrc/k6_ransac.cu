@@ -1,0 +1,401 @@
+// k6_ransac.cu — K6..K9: segment filter + pencil model, the fixed-seed Knuth sampler, the hypotheses x segments
+// scoring grid, and refit + inlier/garbage assignment for up to four vanishing-point structures.
+//
+// Replaces _filter_lines (reference src/interface.cpp:26-32), bounding_box / normalize_lines (src/geometry.cpp:96-112,
+// 258-282), the LinePencilModel constructor (src/line_pencil.cpp:25-32), choice_knuth (src/math_utils.cpp:14-39),
+// RANSAC_Estimator::solve (src/estimator.h:37-78), sample_check / fit / inlier_score / error / fit_optimal
+// (src/line_pencil.cpp:89-140), inclination (src/geometry.cpp:214-229) and estimate_multiple_structures
+// (src/estimator.h:99-145).
+//
+// Everything that decides group membership is evaluated in the reference's float32 operation order: per-hypothesis
+// scores are sequential sums over the observation list, the winner is the first strict maximum in draw order, and the
+// refit scatter matrix is accumulated sequentially.  Tensor cores do not apply (inner dimension 3); the grid runs on the
+// FP32 pipe, one thread per hypothesis with the observations broadcast from shared memory.
+//
+// The sampler reproduces std::mt19937 + libstdc++ generate_canonical<float,24> + Algorithm S exactly.  The uniform
+// stream depends only on the seed, so it is generated once per seed (mt_stream.cu) as k = 2^32 * u (an exact integer,
+// multiple of 256) and shared by every frame; "select" <=> (n - t) * k < (2 - m) * 2^32 in integer arithmetic.
+#include "common.cuh"
+#include "eig.cuh"
+#include "kernels.h"
+
+namespace lrb {
+
+namespace {
+
+// ---- small exact helpers ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ float sum3(float a, float b, float c) { return __fadd_rn(a, __fadd_rn(b, c)); }   // fixed-size-3 reduction order
+
+struct Hyp { float p0, p1, p2, px, py; bool ideal; };
+
+__device__ __forceinline__ Hyp make_hyp(float p0, float p1, float p2)
+{
+    Hyp h; h.p0 = p0; h.p1 = p1; h.p2 = p2;
+    h.ideal = fabsf(p2) < kEps;                                                 // geometry.cpp:219
+    h.px = h.ideal ? p0 : __fdiv_rn(p0, p2);
+    h.py = h.ideal ? p1 : __fdiv_rn(p1, p2);
+    return h;
+}
+
+// 1 - |cos| of the angle between the segment direction and the direction anchor -> vanishing point
+__device__ __forceinline__ float line_error(const Hyp & h, float ax, float ay, float dx, float dy)
+{
+    float vx, vy;
+    if (h.ideal) { vx = h.px; vy = h.py; }
+    else { vx = __fadd_rn(-ax, h.px); vy = __fadd_rn(-ay, h.py); }
+    const float z = __fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy));
+    if (z > 0.f) { const float nr = __fsqrt_rn(z); vx = __fdiv_rn(vx, nr); vy = __fdiv_rn(vy, nr); }
+    const float inc = fabsf(__fadd_rn(__fmul_rn(vx, dx), __fmul_rn(vy, dy)));
+    return __fadd_rn(-inc, 1.0f);
+}
+
+__device__ __forceinline__ void cross3(const float * A, const float * B, float & p0, float & p1, float & p2)
+{
+    p0 = __fsub_rn(__fmul_rn(A[1], B[2]), __fmul_rn(A[2], B[1]));
+    p1 = __fsub_rn(__fmul_rn(A[2], B[0]), __fmul_rn(A[0], B[2]));
+    p2 = __fsub_rn(__fmul_rn(A[0], B[1]), __fmul_rn(A[1], B[0]));
+}
+
+// block-wide exclusive scan of 0/1 flags (blockDim = 1024); returns position, total through `total`
+__device__ __forceinline__ int block_scan_flag(int flag, int * wsum, int & total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const unsigned m = __ballot_sync(0xffffffffu, flag);
+    const int inw = __popc(m & ((1u << lane) - 1));
+    if (lane == 0) wsum[warp] = __popc(m);
+    __syncthreads();
+    if (warp == 0) {
+        int v = lane < nw ? wsum[lane] : 0;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, s); if (lane >= s) v += u; }
+        wsum[lane] = v;
+    }
+    __syncthreads();
+    const int pos = inw + (warp ? wsum[warp - 1] : 0);
+    total = wsum[nw - 1];
+    __syncthreads();
+    return pos;
+}
+
+// ---- K6: filter + bounding box + pencil model --------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCtrl * ctrl, float min_length, int rounds_total)
+{
+    __shared__ int wsum[32];
+    __shared__ float red[4][32];
+    __shared__ int s_base;
+    const int slot = blockIdx.x;
+    FrameCtrl & C = ctrl[slot];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const size_t ko = (size_t)slot * K.cap, lo = (size_t)slot * L.cap;
+    const int ncomp = C.n_comp;
+    SegRec * seg = reinterpret_cast<SegRec *>(L.seg) + lo;
+    const SegRec * raw = reinterpret_cast<const SegRec *>(K.seg) + ko;
+    if (t == 0) s_base = 0;
+    __syncthreads();
+    if (ncomp < 2) {                                                            // interface.cpp:50-54
+        if (t == 0) { C.n_lines = 0; C.num_obs = 0; }
+        return;
+    }
+    const float ml = fmaxf(min_length, kLineMinLength);                         // interface.cpp:29
+    float mnx = INFINITY, mny = INFINITY, mxx = -INFINITY, mxy = -INFINITY;
+    for (int i0 = 0; i0 < ncomp; i0 += 1024) {
+        const int i = i0 + t;
+        int keep = 0; SegRec s;
+        if (i < ncomp) {
+            s = raw[i];
+            const float x = __fsub_rn(s.x2, s.x1), y = __fsub_rn(s.y2, s.y1);
+            const float len = __fsqrt_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)));      // geometry.cpp:90-93
+            keep = (len > ml) && (s.err < kLineMaxErr);
+        }
+        int total;
+        const int pos = s_base + block_scan_flag(keep, wsum, total);
+        if (keep) {
+            if (pos < L.cap) {
+                seg[pos] = s;
+                mnx = fminf(mnx, fminf(s.x1, s.x2)); mxx = fmaxf(mxx, fmaxf(s.x1, s.x2));
+                mny = fminf(mny, fminf(s.y1, s.y2)); mxy = fmaxf(mxy, fmaxf(s.y1, s.y2));
+            } else C.line_overflow = 1;
+        }
+        if (t == 0) s_base += total;
+        __syncthreads();
+    }
+    const int N = min(s_base, L.cap);
+    // bounding box of all endpoints (geometry.cpp:96-112): min/max are exact, any order
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, s)); mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, s));
+        mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, s)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, s));
+    }
+    if (lane == 0) { red[0][warp] = mnx; red[1][warp] = mny; red[2][warp] = mxx; red[3][warp] = mxy; }
+    __syncthreads();
+    mnx = red[0][0]; mny = red[1][0]; mxx = red[2][0]; mxy = red[3][0];
+    for (int w = 1; w < 32; ++w) { mnx = fminf(mnx, red[0][w]); mny = fminf(mny, red[1][w]); mxx = fmaxf(mxx, red[2][w]); mxy = fmaxf(mxy, red[3][w]); }
+    const float sx = __fsub_rn(mxx, mnx), sy = __fsub_rn(mxy, mny);
+    const float cx = __fadd_rn(mnx, __fmul_rn(0.5f, sx)), cy = __fadd_rn(mny, __fmul_rn(0.5f, sy));   // geometry.cpp:272-276
+    const float scale = fmaxf(sx, sy);                                                                // bbox_size().maxCoeff()
+    if (t == 0) {
+        C.n_lines = N; C.num_obs = N; C.n_obs[0] = N; C.n_solves = 0;
+        C.bbox[0] = mnx; C.bbox[1] = mny; C.bbox[2] = mxx; C.bbox[3] = mxy; C.cx = cx; C.cy = cy; C.scale = scale;
+    }
+    for (int i = t; i < N; i += 1024) {
+        const SegRec s = seg[i];
+        // normalize_lines geometry.cpp:258-270
+        const float x1 = __fdiv_rn(__fsub_rn(s.x1, cx), scale), y1 = __fdiv_rn(__fsub_rn(s.y1, cy), scale);
+        const float x2 = __fdiv_rn(__fsub_rn(s.x2, cx), scale), y2 = __fdiv_rn(__fsub_rn(s.y2, cy), scale);
+        // homogeneous geometry.cpp:64-69: (x1,y1,1) x (x2,y2,1), then unit length
+        const float hx = __fsub_rn(__fmul_rn(y1, 1.f), __fmul_rn(1.f, y2));
+        const float hy = __fsub_rn(__fmul_rn(1.f, x2), __fmul_rn(x1, 1.f));
+        const float hz = __fsub_rn(__fmul_rn(x1, y2), __fmul_rn(y1, x2));
+        const float nrm = __fsqrt_rn(sum3(__fmul_rn(hx, hx), __fmul_rn(hy, hy), __fmul_rn(hz, hz)));
+        L.h[(lo + i) * 3 + 0] = __fdiv_rn(hx, nrm); L.h[(lo + i) * 3 + 1] = __fdiv_rn(hy, nrm); L.h[(lo + i) * 3 + 2] = __fdiv_rn(hz, nrm);
+        L.anchor[(lo + i) * 2 + 0] = __fdiv_rn(__fadd_rn(x2, x1), 2.f); L.anchor[(lo + i) * 2 + 1] = __fdiv_rn(__fadd_rn(y2, y1), 2.f);
+        const float ddx = __fsub_rn(x2, x1), ddy = __fsub_rn(y2, y1);
+        const float ln = __fsqrt_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)));
+        L.len[lo + i] = ln;
+        L.dir[(lo + i) * 2 + 0] = __fdiv_rn(ddx, ln); L.dir[(lo + i) * 2 + 1] = __fdiv_rn(ddy, ln);
+        L.inlier[lo + i] = -1; L.garbage[lo + i] = 0; L.obs[lo + i] = i;
+    }
+}
+
+// ---- K7: Knuth Algorithm-S 2-subsets from the shared uniform stream ------------------------------------------------------
+// One warp per frame walks the stream once, 32 positions per step; the chain state (sample start o, picks so far m)
+// lives in registers, the stream is read strictly forward with the next chunks already in flight.
+constexpr int SMP_AHEAD = 8;
+
+__global__ void __launch_bounds__(32) k_sampler(Lines L, FrameCtrl * ctrl, const unsigned * __restrict__ stream,
+                                               unsigned long long stream_len, int solve, int T)
+{
+    const int slot = blockIdx.x;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    const int lane = threadIdx.x;
+    const long long n = C.n_obs[solve];
+    int * pairs = L.pairs + (size_t)slot * 2 * T;
+    unsigned long long o = C.stream_pos;            // start of the current sample
+    unsigned long long cur = o;                     // first unconsumed stream position
+    unsigned long long base = o & ~31ull;
+    int m = 0, s0 = 0, done = 0;
+    unsigned kk[SMP_AHEAD];
+#pragma unroll
+    for (int a = 0; a < SMP_AHEAD; ++a) { const unsigned long long p = base + 32ull * a + lane; kk[a] = p < stream_len ? __ldg(stream + p) : 0u; }
+    bool overflow = false;
+    while (done < T) {
+#pragma unroll
+        for (int a = 0; a < SMP_AHEAD; ++a) {
+            if (done >= T) break;
+            const unsigned k = kk[a];
+            const unsigned long long p = base + lane;
+            if (base + 32 > stream_len) { overflow = true; done = T; break; }
+            // refill this register with the chunk SMP_AHEAD steps ahead before the dependent chain below
+            { const unsigned long long pn = p + 32ull * SMP_AHEAD; kk[a] = pn < stream_len ? __ldg(stream + pn) : 0u; }
+            while (true) {
+                const long long t = (long long)(p - o);                          // draws already made in this sample
+                const bool can = (p >= cur) && (t < n);
+                const bool sel = can && ((unsigned long long)(n - t) * (unsigned long long)k < ((unsigned long long)(2 - m) << 32));
+                const unsigned bm = __ballot_sync(0xffffffffu, sel);
+                if (bm == 0) break;
+                const int l = __ffs(bm) - 1;
+                const unsigned long long pos = base + l;
+                if (m == 0) { s0 = (int)(pos - o); m = 1; cur = pos + 1; }
+                else {
+                    if (lane == 0) { pairs[2 * done] = s0; pairs[2 * done + 1] = (int)(pos - o); }
+                    ++done; m = 0; o = pos + 1; cur = o;
+                    if (done >= T) break;
+                }
+            }
+            base += 32; if (cur < base) cur = base;
+        }
+    }
+    if (lane == 0) { C.stream_pos = o; if (overflow) C.stream_overflow = 1; }
+}
+
+// ---- K8: scoring grid -------------------------------------------------------------------------------------------------
+constexpr int SC_THREADS = 128;
+constexpr int SC_CHUNK = 1024;
+
+__global__ void __launch_bounds__(SC_THREADS) k_score(Lines L, FrameCtrl * ctrl, int solve, int T)
+{
+    __shared__ float4 s_ad[SC_CHUNK];      // anchor.x, anchor.y, dir.x, dir.y
+    __shared__ float s_len[SC_CHUNK];
+    __shared__ unsigned long long s_best[SC_THREADS / 32];
+    const int slot = blockIdx.y;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    const int n = C.n_obs[solve];
+    const size_t lo = (size_t)slot * L.cap;
+    const int * obs = L.obs + lo;
+    const int i = blockIdx.x * SC_THREADS + threadIdx.x;           // draw index
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    bool ok = false; Hyp h = make_hyp(0.f, 0.f, 0.f);
+    if (i < T) {
+        const int * pr = L.pairs + (size_t)slot * 2 * T + 2 * i;
+        const int a = obs[pr[0]], b = obs[pr[1]];
+        const float * A = L.h + (lo + a) * 3; const float * B = L.h + (lo + b) * 3;
+        const float ex = __fsub_rn(A[0], B[0]), ey = __fsub_rn(A[1], B[1]), ez = __fsub_rn(A[2], B[2]);
+        ok = __fsqrt_rn(sum3(__fmul_rn(ex, ex), __fmul_rn(ey, ey), __fmul_rn(ez, ez))) > kDegeneracyTol;   // line_pencil.cpp:89-98
+        float p0, p1, p2; cross3(A, B, p0, p1, p2);                                                     // line_pencil.cpp:101-108
+        h = make_hyp(p0, p1, p2);
+    }
+    float score = 0.f;
+    for (int c0 = 0; c0 < n; c0 += SC_CHUNK) {
+        const int cn = min(SC_CHUNK, n - c0);
+        __syncthreads();
+        for (int k = threadIdx.x; k < cn; k += SC_THREADS) {
+            const int q = obs[c0 + k];
+            const float2 an = *reinterpret_cast<const float2 *>(L.anchor + (lo + q) * 2);
+            const float2 di = *reinterpret_cast<const float2 *>(L.dir + (lo + q) * 2);
+            s_ad[k] = make_float4(an.x, an.y, di.x, di.y);
+            s_len[k] = L.len[lo + q];
+        }
+        __syncthreads();
+        if (ok) {
+#pragma unroll 4
+            for (int k = 0; k < cn; ++k) {
+                const float4 v = s_ad[k];
+                const float e = line_error(h, v.x, v.y, v.z, v.w);
+                const float tt = __fmul_rn(e < kTolInlier ? 1.f : 0.f, s_len[k]);       // line_pencil.cpp:137-140
+                score = (c0 + k == 0) ? tt : __fadd_rn(score, tt);
+            }
+        }
+    }
+    if (i < T) L.scores[((size_t)slot * kMaxModels + solve) * T + i] = ok ? score : -1.f;
+    // first strict maximum in draw order (estimator.h:62-70): max score, then lowest draw index
+    unsigned long long key = (ok && score > 0.f) ? (((unsigned long long)__float_as_uint(score) << 32) | (unsigned)(0xFFFFFFFFu - (unsigned)i)) : 0ull;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { const unsigned long long o = __shfl_xor_sync(0xffffffffu, key, s); key = o > key ? o : key; }
+    if (lane == 0) s_best[warp] = key;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < SC_THREADS / 32; ++w) key = s_best[w] > key ? s_best[w] : key;
+        if (key) atomicMax(&C.best[solve], key);
+    }
+}
+
+// ---- K9: refit on the winner's inliers, assign inliers / garbage, build the next observation list ----------------------
+__global__ void __launch_bounds__(1024) k_refit_assign(Lines L, FrameCtrl * ctrl, int solve, int T)
+{
+    __shared__ int wsum[32];
+    __shared__ float s_cov[9];
+    __shared__ float s_h[3];
+    __shared__ int s_cnt[2];
+    const int slot = blockIdx.x;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    const int t = threadIdx.x;
+    const int n = C.n_obs[solve];
+    const int N = C.n_lines;
+    const size_t lo = (size_t)slot * L.cap;
+    int * obs = L.obs + lo; int * inl = L.tmp + lo;
+
+    // winner -> best_h (recomputed from its pair: same arithmetic as in the scoring kernel)
+    float b0 = 0.f, b1 = 0.f, b2 = 0.f; int win = -1;
+    {
+        const unsigned long long key = C.best[solve];
+        if (key) {
+            win = (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull));
+            const int * pr = L.pairs + (size_t)slot * 2 * T + 2 * win;
+            cross3(L.h + (lo + obs[pr[0]]) * 3, L.h + (lo + obs[pr[1]]) * 3, b0, b1, b2);
+        }
+    }
+    const Hyp hb = make_hyp(b0, b1, b2);
+    // inliers of best_h in observation order (estimator.h:73-76)
+    int ni = 0;
+    for (int k0 = 0; k0 < n; k0 += 1024) {
+        const int k = k0 + t; int f = 0, q = 0;
+        if (k < n) {
+            q = obs[k];
+            f = line_error(hb, L.anchor[(lo + q) * 2], L.anchor[(lo + q) * 2 + 1], L.dir[(lo + q) * 2], L.dir[(lo + q) * 2 + 1]) < kTolInlier;
+        }
+        int total; const int pos = ni + block_scan_flag(f, wsum, total);
+        if (f) inl[pos] = q;
+        ni += total;
+    }
+    __syncthreads();
+    // fit_optimal (line_pencil.cpp:111-128): empty index list => ALL lines of the model
+    const bool all = (ni == 0);
+    const int cnt = all ? N : ni;
+    if (t < 6) {
+        // lower triangle (r >= c) of h^T diag(len) h, each entry a sequential sum of (h_r * len) * h_c
+        const int r = (t == 0) ? 0 : (t < 3 ? 1 : 2);
+        const int c = (t == 0) ? 0 : (t == 1 ? 0 : (t == 2 ? 1 : t - 3));
+        float acc = 0.f;
+        for (int k = 0; k < cnt; ++k) {
+            const int q = all ? k : inl[k];
+            const float v = __fmul_rn(__fmul_rn(L.h[(lo + q) * 3 + r], L.len[lo + q]), L.h[(lo + q) * 3 + c]);
+            acc = (k == 0) ? v : __fadd_rn(acc, v);
+        }
+        s_cov[r * 3 + c] = acc; s_cov[c * 3 + r] = acc;
+    }
+    __syncthreads();
+    if (t == 0) {
+        float eval[3], evec[9];
+        sym_eig<3>(s_cov, eval, evec);
+        int k = 0;
+        for (int i = 1; i < 3; ++i) if (eval[i] < eval[k]) k = i;                 // minCoeff: first minimum
+        s_h[0] = evec[k * 3]; s_h[1] = evec[k * 3 + 1]; s_h[2] = evec[k * 3 + 2];
+        C.winner[solve] = win;
+        C.best_h[solve][0] = b0; C.best_h[solve][1] = b1; C.best_h[solve][2] = b2;
+        C.refined[solve][0] = s_h[0]; C.refined[solve][1] = s_h[1]; C.refined[solve][2] = s_h[2];
+        s_cnt[0] = 0; s_cnt[1] = 0;
+    }
+    __syncthreads();
+    const Hyp hr = make_hyp(s_h[0], s_h[1], s_h[2]);
+    // estimator.h:127-138: inliers get the structure index, near misses become garbage
+    int n_in = 0, n_gb = 0;
+    for (int k = t; k < n; k += 1024) {
+        const int q = obs[k];
+        const float e = line_error(hr, L.anchor[(lo + q) * 2], L.anchor[(lo + q) * 2 + 1], L.dir[(lo + q) * 2], L.dir[(lo + q) * 2 + 1]);
+        if (e < kTolInlier) { L.inlier[lo + q] = solve; ++n_in; }
+        else if (e < kTolGarbage) { L.garbage[lo + q] = 1; ++n_gb; }
+    }
+    atomicAdd(&s_cnt[0], n_in); atomicAdd(&s_cnt[1], n_gb);
+    __syncthreads();
+    // next observation list: nonzero(inlier < 0 && garbage == 0) in index order (estimator.h:124, utils.h:16-30)
+    int no = 0;
+    for (int i0 = 0; i0 < N; i0 += 1024) {
+        const int i = i0 + t; int f = 0;
+        if (i < N) f = (L.inlier[lo + i] < 0) && (L.garbage[lo + i] == 0);
+        int total; const int pos = no + block_scan_flag(f, wsum, total);
+        if (f) obs[pos] = i;
+        no += total;
+    }
+    if (t == 0) {
+        C.num_obs -= s_cnt[0] + s_cnt[1];
+        C.n_solves = solve + 1;
+        if (solve + 1 < kMaxModels) C.n_obs[solve + 1] = no;
+    }
+}
+
+// group ids as the reference reports them: garbage lines end up unassigned (estimator.h:142)
+__global__ void k_finalize(Lines L, FrameCtrl * ctrl)
+{
+    const int slot = blockIdx.y;
+    const int N = ctrl[slot].n_lines;
+    const size_t lo = (size_t)slot * L.cap;
+    SegRec * seg = reinterpret_cast<SegRec *>(L.seg) + lo;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x)
+        seg[i].group_id = L.garbage[lo + i] ? -1 : L.inlier[lo + i];
+}
+
+} // namespace
+
+void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, cudaStream_t st)
+{
+    k_filter_model<<<n_slots, 1024, 0, st>>>(K, L, ctrl, min_length, rounds_total);
+}
+
+void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
+                   int T, cudaStream_t st)
+{
+    for (int k = 0; k < kMaxModels; ++k) {
+        k_sampler<<<n_slots, 32, 0, st>>>(L, ctrl, stream, stream_len, k, T);
+        dim3 gs((T + SC_THREADS - 1) / SC_THREADS, n_slots);
+        k_score<<<gs, SC_THREADS, 0, st>>>(L, ctrl, k, T);
+        k_refit_assign<<<n_slots, 1024, 0, st>>>(L, ctrl, k, T);
+    }
+    dim3 gf(8, n_slots);
+    k_finalize<<<gf, 256, 0, st>>>(L, ctrl);
+}
+
+} // namespace lrb

@@ -1,0 +1,38 @@
+// kernels.h — host-callable launchers of the sm_100a kernels (internal; the public C ABI is include/librectify_b200.h)
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include "common.cuh"
+
+namespace lrb {
+
+// k1_grad.cu
+void launch_grad(const CUtensorMap & tmap_img, const Planes & P, FrameCtrl * ctrl, int n_slots, cudaStream_t st);
+int  grad_tile_w();
+int  grad_tile_h();
+// k2_nms.cu
+void launch_frame_init(const Seeds & S, FrameCtrl * ctrl, int n_slots, cudaStream_t st);
+void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, const Planes & P, const Seeds & S,
+                FrameCtrl * ctrl, int n_slots, cudaStream_t st);
+void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st);
+void nms_tile_dims(int * mw, int * mh, int * bw, int * bh);
+// k4_flood.cu
+void launch_flood_rounds(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint,
+                         int round_begin, int round_end, unsigned epoch_first, cudaStream_t st);
+void launch_flood_serial(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots,
+                         unsigned epoch_first, unsigned epoch_serial, cudaStream_t st);
+// k5_fit.cu
+void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int rounds_total, cudaStream_t st);
+void launch_labels(const Planes & P, const Comps & K, FrameCtrl * ctrl, int * labels, int slot, cudaStream_t st);
+// k6_ransac.cu
+void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, cudaStream_t st);
+void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
+                   int T, cudaStream_t st);
+// mt_stream.cu
+void launch_mt_stream(unsigned seed, unsigned * stream, unsigned long long n, cudaStream_t st);
+// ingest.cu
+void launch_ingest(const float * src, long long src_pitch, long long src_frame_stride, float * dst, int dst_pitch,
+                   size_t dst_stride, int w, int h, int n_slots, cudaStream_t st);
+void launch_fill_u32(unsigned * p, size_t n, unsigned v, cudaStream_t st);
+
+} // namespace lrb
