@@ -1,0 +1,130 @@
+/* librectify_b200.h — C ABI of the B200 engine underneath librectify.h.
+ *
+ * librectify.h is the drop-in surface (the reference's six functions).  This header is the thin C-ABI layer the
+ * north star asks for between host code and the sm_100a kernels: plain pointers and sizes, no C++ or torch types.
+ * It adds what the reference's one-image-per-call API cannot express on a GPU:
+ *   - an explicit engine (one CUDA device, one stream, one workspace of `slots` frame slots),
+ *   - batched calls over frames already resident in device memory (or in host memory),
+ *   - a stage window for parity tests (every intermediate the reference computes can be fetched),
+ *   - per-stage device timings for the roofline report.
+ * Every function returns 0 on success and a negative code on failure; lrb_last_error() then describes it.
+ * Nothing here falls back to the CPU: without a CUDA device lrb_engine_create fails.
+ */
+#pragma once
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+  #define LRB_API __declspec(dllexport)
+#else
+  #define LRB_API __attribute__((visibility("default")))
+#endif
+
+/* Same layout as librectify::LineSegment / Point / ImageTransform / RectificationConfig
+ * (reference src/librectify.h:44-54,60-63,79-86,137-150); repeated as C structs so that C callers and FFI generators
+ * (ctypes, cgo, JNI) can use this header without the C++ one. */
+typedef struct lrb_segment { float x1, y1, x2, y2, weight, err; int group_id; } lrb_segment;
+typedef struct lrb_point { float x, y, z; } lrb_point;
+typedef struct lrb_transform {
+    int width, height;
+    lrb_point top_left, top_right, bottom_left, bottom_right, horizontal_vp, vertical_vp;
+} lrb_transform;
+typedef struct lrb_config {
+    float vertical_vp_angular_tolerance, vertical_vp_min_distance; int v_strategy;
+    float horizontal_vp_min_distance; int h_strategy;
+} lrb_config;
+
+/* Per-frame outcome of the detection + grouping pipeline. */
+typedef struct lrb_frame_info {
+    int n_lines;          /* filtered segments (0 when the reference would return nullptr) */
+    int n_seeds;          /* NMS peaks */
+    int n_components;     /* kept components = raw segments */
+    int n_pixels;         /* pixels in kept components */
+    int flood_rounds;     /* speculative rounds that did work */
+    int flood_fallback;   /* 1 if the serial fallback flood was needed */
+    int n_solves;         /* vanishing-point structures estimated (<= 4) */
+    int n_obs[4];         /* observations per solve: the scoring grid is 10^4 x n_obs[k] */
+    float max_magnitude;
+} lrb_frame_info;
+
+typedef struct lrb_engine lrb_engine;
+
+LRB_API const char * lrb_last_error(void);
+LRB_API const char * lrb_version(void);
+
+/* Seed of the sampler's mt19937 for engines created afterwards and for the drop-in API (the reference seeds from
+ * std::random_device, reference src/estimator.h:35; a fixed seed — default 0 — makes the library deterministic). */
+LRB_API void lrb_set_seed(unsigned seed);
+
+/* One engine = one device + one stream + workspace for `slots` frames processed per launch group. */
+LRB_API int  lrb_engine_create(int device, int slots, lrb_engine ** out);
+LRB_API void lrb_engine_destroy(lrb_engine * e);
+LRB_API int  lrb_engine_slots(const lrb_engine * e);
+
+/* find_line_segment_groups for n_frames frames of equal size.
+ *   frames        first pixel of frame 0; device memory for _device, host memory (pageable or pinned) for _host
+ *   pitch         elements between rows (may be negative for _host with n_frames == 1, reference librectify.h:15-18)
+ *   frame_stride  elements between frames
+ *   info          host array [n_frames]
+ *   lines         host array [n_frames * lines_cap] or NULL; frame i's segments start at lines + i * lines_cap
+ * A frame with more than lines_cap segments reports its true n_lines and is truncated in `lines`. */
+LRB_API int lrb_detect_device(lrb_engine * e, const float * frames, int n_frames, int width, int height,
+                              long long pitch, long long frame_stride, float min_length,
+                              lrb_frame_info * info, lrb_segment * lines, int lines_cap);
+LRB_API int lrb_detect_host(lrb_engine * e, const float * frames, int n_frames, int width, int height,
+                            long long pitch, long long frame_stride, float min_length,
+                            lrb_frame_info * info, lrb_segment * lines, int lines_cap);
+
+/* detect + compute_rectification_transform per frame (the whole hot path); cfg is one config for all frames
+ * (n_cfg == 1) or one per frame cycled modulo n_cfg.  transforms: host array [n_frames]. */
+LRB_API int lrb_rectify_device(lrb_engine * e, const float * frames, int n_frames, int width, int height,
+                               long long pitch, long long frame_stride, float min_length,
+                               const lrb_config * cfg, int n_cfg, lrb_transform * transforms, lrb_frame_info * info);
+LRB_API int lrb_rectify_host(lrb_engine * e, const float * frames, int n_frames, int width, int height,
+                             long long pitch, long long frame_stride, float min_length,
+                             const lrb_config * cfg, int n_cfg, lrb_transform * transforms, lrb_frame_info * info);
+
+/* Host-side corner solve on caller-provided segments (pointer form of compute_rectification_transform etc.). */
+LRB_API void lrb_compute_transform(const lrb_segment * lines, int n_lines, int width, int height,
+                                   const lrb_config * cfg, lrb_transform * out);
+LRB_API void lrb_compute_transform_from_vp(int width, int height, const lrb_point * vp_h, const lrb_point * vp_v,
+                                           lrb_transform * out);
+LRB_API void lrb_fit_vanishing_point(const lrb_segment * lines, int n_lines, int group, lrb_point * out);
+LRB_API void lrb_assign_to_group(const lrb_segment * lines, int n_lines, lrb_segment * new_lines, int n_new_lines,
+                                 float angular_tolerance_deg);
+
+/* ---- stage window (parity tests): contents of slot `slot` after the last lrb_detect_* call on this engine --------- */
+enum lrb_stage {
+    LRB_ST_DX = 0, LRB_ST_DY, LRB_ST_MAG,        /* float32 [h*w] */
+    LRB_ST_BIN, LRB_ST_MASK8,                    /* uint8   [h*w] */
+    LRB_ST_SEEDS,                                /* int32   [n_seeds*2] (row, col) in processing order */
+    LRB_ST_LABELS,                               /* int32   [h*w] kept-component index or -1 */
+    LRB_ST_COMP_SIZES,                           /* int32   [n_components] */
+    LRB_ST_RAW_SEGS,                             /* lrb_segment [n_components] */
+    LRB_ST_MODEL_H, LRB_ST_MODEL_ANCHOR, LRB_ST_MODEL_DIR, LRB_ST_MODEL_LEN,   /* float32 [n_lines*3|2|2|1] */
+    LRB_ST_MODEL_BBOX,                           /* float32 [7]: minx miny maxx maxy cx cy scale */
+    LRB_ST_PAIRS,                                /* int32   [10000*2]: samples of the LAST solve */
+    LRB_ST_SCORES,                               /* float32 [4*10000] (-1 = rejected sample) */
+    LRB_ST_RANSAC,                               /* int32 winner[4], float best_h[12], float refined[12] = 28 words */
+    LRB_ST_STREAM                                /* uint32 [count]: head of the uniform stream (k = 2^32 u) */
+};
+LRB_API long long lrb_stage_fetch(lrb_engine * e, int slot, int stage, void * dst, size_t dst_bytes);
+
+/* ---- per-stage device timings (CUDA events on the engine's stream) ---------------------------------------------- */
+enum lrb_timer { LRB_T_INGEST = 0, LRB_T_GRAD, LRB_T_NMS, LRB_T_SEEDS, LRB_T_FLOOD, LRB_T_FIT, LRB_T_MODEL,
+                 LRB_T_RANSAC, LRB_T_READBACK, LRB_T_COUNT };
+LRB_API void lrb_profile_enable(lrb_engine * e, int on);
+LRB_API void lrb_profile_reset(lrb_engine * e);
+/* ms[LRB_T_COUNT]: summed device milliseconds per stage; groups: launch groups timed; kernels: kernels launched */
+LRB_API void lrb_profile_read(lrb_engine * e, double * ms, long long * groups, long long * kernels);
+
+/* One uniform-stream sample run, for the sampler known-answer tests: `count` 2-subsets of [0,n) from the start of
+ * the stream; returns the number of draws consumed (or negative on error). pairs: host int32 [count*2]. */
+LRB_API long long lrb_sample_pairs(lrb_engine * e, int n, int count, int * pairs);
+
+#ifdef __cplusplus
+}
+#endif

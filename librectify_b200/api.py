@@ -1,0 +1,290 @@
+"""Python host-side mirror of the C ABI (include/librectify.h + include/librectify_b200.h) over ctypes.
+
+Names and argument meaning follow the reference's C API (reference src/librectify.h:111-222): ``find_line_segment_groups``
+takes a float32 grayscale image and returns the grouped segments, ``compute_rectification_transform`` turns them into the
+warped image corners.  ``Engine`` exposes the batched entry points for frames resident in device memory (torch CUDA
+tensors are passed by ``data_ptr()`` — torch is plumbing here, the work happens in librectify_b200.so).
+
+The shared library is the product; this module never computes anything itself and raises if the library is missing or
+no CUDA device is present (there is no CPU fallback).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "librectify_b200.so")
+
+ROTATE_H, ROTATE_V, RECTIFY, KEEP = 0, 1, 2, 3
+RANSAC_ITER = 10000
+
+SEG_DTYPE = np.dtype([("x1", "<f4"), ("y1", "<f4"), ("x2", "<f4"), ("y2", "<f4"),
+                      ("weight", "<f4"), ("err", "<f4"), ("group_id", "<i4")])
+TF_DTYPE = np.dtype([("width", "<i4"), ("height", "<i4"), ("top_left", "<f4", 3), ("top_right", "<f4", 3),
+                     ("bottom_left", "<f4", 3), ("bottom_right", "<f4", 3), ("horizontal_vp", "<f4", 3),
+                     ("vertical_vp", "<f4", 3)])
+CFG_DTYPE = np.dtype([("vertical_vp_angular_tolerance", "<f4"), ("vertical_vp_min_distance", "<f4"), ("v_strategy", "<i4"),
+                      ("horizontal_vp_min_distance", "<f4"), ("h_strategy", "<i4")])
+INFO_DTYPE = np.dtype([("n_lines", "<i4"), ("n_seeds", "<i4"), ("n_components", "<i4"), ("n_pixels", "<i4"),
+                       ("flood_rounds", "<i4"), ("flood_fallback", "<i4"), ("n_solves", "<i4"), ("n_obs", "<i4", 4),
+                       ("max_magnitude", "<f4")])
+assert SEG_DTYPE.itemsize == 28 and TF_DTYPE.itemsize == 80 and CFG_DTYPE.itemsize == 20 and INFO_DTYPE.itemsize == 48
+
+STAGES = dict(dx=0, dy=1, mag=2, bin=3, mask8=4, seeds=5, labels=6, comp_sizes=7, raw_segs=8, model_h=9, model_anchor=10,
+              model_dir=11, model_len=12, model_bbox=13, pairs=14, scores=15, ransac=16, stream=17)
+TIMERS = ("ingest", "grad", "nms", "seeds", "flood", "fit", "model", "ransac", "readback")
+
+
+class LibrectifyError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library(path: str | None = None):
+    """dlopen the in-tree shared object (built by librectify_b200/build.py). No fallback if it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise LibrectifyError(f"{p} not found: build it with `python -m librectify_b200.build` (there is no CPU fallback)")
+    lib = C.CDLL(p)
+    vp, ip, fp, ll = C.c_void_p, C.c_int, C.c_float, C.c_longlong
+    lib.lrb_last_error.restype = C.c_char_p
+    lib.lrb_version.restype = C.c_char_p
+    lib.lrb_set_seed.argtypes = [C.c_uint]; lib.lrb_set_seed.restype = None
+    lib.lrb_engine_create.argtypes = [ip, ip, C.POINTER(vp)]
+    lib.lrb_engine_destroy.argtypes = [vp]; lib.lrb_engine_destroy.restype = None
+    lib.lrb_engine_slots.argtypes = [vp]
+    for name in ("lrb_detect_device", "lrb_detect_host"):
+        getattr(lib, name).argtypes = [vp, vp, ip, ip, ip, ll, ll, fp, vp, vp, ip]
+    for name in ("lrb_rectify_device", "lrb_rectify_host"):
+        getattr(lib, name).argtypes = [vp, vp, ip, ip, ip, ll, ll, fp, vp, ip, vp, vp]
+    lib.lrb_compute_transform.argtypes = [vp, ip, ip, ip, vp, vp]; lib.lrb_compute_transform.restype = None
+    lib.lrb_compute_transform_from_vp.argtypes = [ip, ip, vp, vp, vp]; lib.lrb_compute_transform_from_vp.restype = None
+    lib.lrb_fit_vanishing_point.argtypes = [vp, ip, ip, vp]; lib.lrb_fit_vanishing_point.restype = None
+    lib.lrb_assign_to_group.argtypes = [vp, ip, vp, ip, fp]; lib.lrb_assign_to_group.restype = None
+    lib.lrb_stage_fetch.argtypes = [vp, ip, ip, vp, C.c_size_t]; lib.lrb_stage_fetch.restype = ll
+    lib.lrb_profile_enable.argtypes = [vp, ip]; lib.lrb_profile_enable.restype = None
+    lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None
+    lib.lrb_profile_read.argtypes = [vp, vp, vp, vp]; lib.lrb_profile_read.restype = None
+    lib.lrb_sample_pairs.argtypes = [vp, ip, ip, vp]; lib.lrb_sample_pairs.restype = ll
+    # the drop-in symbols (reference names)
+    lib.find_line_segment_groups.restype = vp
+    lib.find_line_segment_groups.argtypes = [vp, ip, ip, ip, fp, C.c_bool, ip, C.POINTER(ip)]
+    lib.release_line_segments.argtypes = [C.POINTER(vp)]; lib.release_line_segments.restype = None
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _err(lib) -> str:
+    return (lib.lrb_last_error() or b"").decode()
+
+
+def make_config(vertical_vp_angular_tolerance=40.0, vertical_vp_min_distance=1.5, v_strategy=RECTIFY,
+                horizontal_vp_min_distance=1.5, h_strategy=RECTIFY) -> np.ndarray:
+    """RectificationConfig with the reference's defaults (reference src/librectify.h:137-150)."""
+    c = np.zeros(1, CFG_DTYPE)
+    c[0] = (vertical_vp_angular_tolerance, vertical_vp_min_distance, v_strategy, horizontal_vp_min_distance, h_strategy)
+    return c
+
+
+def set_seed(seed: int) -> None:
+    load_library().lrb_set_seed(C.c_uint(seed))
+
+
+# ---- the reference's functions ----------------------------------------------------------------------------------------
+def find_line_segment_groups(image: np.ndarray, min_length: float, refine: bool = False, num_threads: int = -1,
+                             stride: int | None = None, flipped: bool = False):
+    """reference src/interface.cpp:35-80 through the drop-in symbol.  image: float32 [H, W] host array.
+    Returns a SEG_DTYPE array, or None where the reference returns nullptr."""
+    lib = load_library()
+    assert image.dtype == np.float32 and image.ndim == 2
+    h, w = image.shape
+    if stride is None:
+        assert image.flags.c_contiguous
+        stride = w
+    base = image.ctypes.data
+    if flipped:
+        base += 4 * stride * (h - 1); stride = -stride
+    n = C.c_int(-1)
+    ptr = lib.find_line_segment_groups(C.c_void_p(base), w, h, stride, C.c_float(min_length), bool(refine), int(num_threads), C.byref(n))
+    if not ptr:
+        if n.value != 0:
+            raise LibrectifyError("null result with n_lines != 0")
+        msg = _err(lib)
+        if msg and ("CUDA" in msg or "failed" in msg or "capacity" in msg):
+            raise LibrectifyError(msg)
+        return None
+    out = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_byte)), shape=(n.value * 28,)).view(SEG_DTYPE).copy()
+    p = C.c_void_p(ptr)
+    lib.release_line_segments(C.byref(p))
+    assert not p.value
+    return out
+
+
+def compute_rectification_transform(lines: np.ndarray, width: int, height: int, cfg: np.ndarray | None = None) -> np.ndarray:
+    """reference src/interface.cpp:122-208 (host).  Returns a TF_DTYPE scalar array."""
+    lib = load_library()
+    cfg = make_config() if cfg is None else cfg
+    lines = np.ascontiguousarray(lines, SEG_DTYPE)
+    out = np.zeros(1, TF_DTYPE)
+    lib.lrb_compute_transform(lines.ctypes.data, len(lines), width, height, cfg.ctypes.data, out.ctypes.data)
+    return out[0]
+
+
+def compute_rectification_transform_from_vp(width, height, vp_h, vp_v) -> np.ndarray:
+    lib = load_library()
+    a = np.asarray(vp_h, np.float32); b = np.asarray(vp_v, np.float32)
+    out = np.zeros(1, TF_DTYPE)
+    lib.lrb_compute_transform_from_vp(width, height, a.ctypes.data, b.ctypes.data, out.ctypes.data)
+    return out[0]
+
+
+def fit_vanishing_point(lines: np.ndarray, group: int):
+    lib = load_library()
+    lines = np.ascontiguousarray(lines, SEG_DTYPE)
+    out = np.zeros(3, np.float32)
+    lib.lrb_fit_vanishing_point(lines.ctypes.data, len(lines), group, out.ctypes.data)
+    return tuple(float(v) for v in out)
+
+
+def assign_to_group(lines: np.ndarray, new_lines: np.ndarray, angular_tolerance: float) -> np.ndarray:
+    lib = load_library()
+    lines = np.ascontiguousarray(lines, SEG_DTYPE)
+    new = np.ascontiguousarray(new_lines, SEG_DTYPE).copy()
+    lib.lrb_assign_to_group(lines.ctypes.data, len(lines), new.ctypes.data, len(new), C.c_float(angular_tolerance))
+    return new
+
+
+def tform_vec(t) -> np.ndarray:
+    """flat float64 vector in the golden-fixture layout (tests/util.py)."""
+    return np.array([t["width"], t["height"], *t["top_left"], *t["top_right"], *t["bottom_left"], *t["bottom_right"],
+                     *t["horizontal_vp"], *t["vertical_vp"]], dtype=np.float64)
+
+
+# ---- the engine (batched C ABI) ------------------------------------------------------------------------------------------
+class Engine:
+    """One CUDA device + stream + workspace of ``slots`` frames (include/librectify_b200.h)."""
+
+    def __init__(self, device: int = 0, slots: int = 1):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.lrb_engine_create(device, slots, C.byref(h))
+        if rc != 0:
+            raise LibrectifyError(_err(self.lib))
+        self.h = h
+        self.device = device
+        self.slots = slots
+        self.w = self.h_ = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lrb_engine_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise LibrectifyError(_err(self.lib))
+
+    @staticmethod
+    def _frames_args(frames):
+        """(pointer, n, h, w, pitch, frame_stride, on_device, keepalive) for a numpy array or a torch tensor [n,h,w] / [h,w]."""
+        if isinstance(frames, np.ndarray):
+            a = frames if frames.ndim == 3 else frames[None]
+            assert a.dtype == np.float32 and a.strides[2] == 4 and a.strides[1] % 4 == 0
+            fs = a.strides[0] // 4 if a.shape[0] > 1 else a.shape[1] * (a.strides[1] // 4)
+            return a.ctypes.data, a.shape[0], a.shape[1], a.shape[2], a.strides[1] // 4, fs, False, a
+        import torch
+        t = frames if frames.dim() == 3 else frames[None]
+        assert t.dtype == torch.float32 and t.stride(2) == 1
+        fs = t.stride(0) if t.shape[0] > 1 else t.shape[1] * t.stride(1)
+        return t.data_ptr(), t.shape[0], t.shape[1], t.shape[2], t.stride(1), fs, t.is_cuda, t
+
+    def detect(self, frames, min_length: float, lines_cap: int = 4096):
+        """find_line_segment_groups over a batch. Returns (info[n] INFO_DTYPE, list of SEG_DTYPE arrays)."""
+        ptr, n, h, w, pitch, fs, dev, keep = self._frames_args(frames)
+        info = np.zeros(n, INFO_DTYPE)
+        lines = np.zeros((n, lines_cap), SEG_DTYPE)
+        fn = self.lib.lrb_detect_device if dev else self.lib.lrb_detect_host
+        self._check(fn(self.h, ptr, n, w, h, pitch, fs, C.c_float(min_length), info.ctypes.data, lines.ctypes.data, lines_cap))
+        self.w, self.h_ = w, h
+        if int(info["n_lines"].max(initial=0)) > lines_cap:
+            return self.detect(frames, min_length, int(info["n_lines"].max()))
+        return info, [lines[i, :info["n_lines"][i]].copy() for i in range(n)]
+
+    def rectify(self, frames, min_length: float, cfg: np.ndarray | None = None):
+        """detect + compute_rectification_transform per frame. Returns (transforms[n] TF_DTYPE, info[n])."""
+        ptr, n, h, w, pitch, fs, dev, keep = self._frames_args(frames)
+        cfg = make_config() if cfg is None else np.ascontiguousarray(cfg, CFG_DTYPE)
+        info = np.zeros(n, INFO_DTYPE)
+        tf = np.zeros(n, TF_DTYPE)
+        fn = self.lib.lrb_rectify_device if dev else self.lib.lrb_rectify_host
+        self._check(fn(self.h, ptr, n, w, h, pitch, fs, C.c_float(min_length), cfg.ctypes.data, len(cfg), tf.ctypes.data, info.ctypes.data))
+        self.w, self.h_ = w, h
+        return tf, info
+
+    # stage window ------------------------------------------------------------------------------------------------------
+    def fetch(self, stage: str, slot: int = 0, count: int | None = None) -> np.ndarray:
+        w, h = self.w, self.h_
+        kinds = dict(dx=(np.float32, (h, w)), dy=(np.float32, (h, w)), mag=(np.float32, (h, w)), bin=(np.uint8, (h, w)),
+                     mask8=(np.uint8, (h, w)), labels=(np.int32, (h, w)), model_bbox=(np.float32, (7,)),
+                     pairs=(np.int32, (RANSAC_ITER, 2)), scores=(np.float32, (4, RANSAC_ITER)), ransac=(np.int32, (28,)))
+        if stage in kinds:
+            dt, shape = kinds[stage]
+            buf = np.zeros(shape, dt)
+        elif stage == "stream":
+            buf = np.zeros(count or 16, np.uint32)
+        else:
+            cap = count if count is not None else (w * h // 4 + 4096)
+            dt = {"seeds": np.int32, "comp_sizes": np.int32, "raw_segs": SEG_DTYPE}.get(stage, np.float32)
+            mult = {"seeds": 2, "model_h": 3, "model_anchor": 2, "model_dir": 2}.get(stage, 1)
+            buf = np.zeros(cap * mult, dt)
+        got = self.lib.lrb_stage_fetch(self.h, slot, STAGES[stage], buf.ctypes.data, buf.nbytes)
+        if got < 0:
+            raise LibrectifyError(_err(self.lib))
+        if stage in kinds:
+            return buf
+        out = buf[: got // buf.itemsize]
+        if stage == "seeds":
+            return out.reshape(-1, 2)
+        if stage in ("model_h",):
+            return out.reshape(-1, 3)
+        if stage in ("model_anchor", "model_dir"):
+            return out.reshape(-1, 2)
+        return out
+
+    def ransac_trace(self, slot: int = 0) -> dict:
+        raw = self.fetch("ransac", slot)
+        return dict(winner=raw[:4].copy(), best_h=raw[4:16].view(np.float32).reshape(4, 3).copy(),
+                    refined=raw[16:28].view(np.float32).reshape(4, 3).copy())
+
+    def sample_pairs(self, n: int, count: int):
+        pairs = np.zeros((count, 2), np.int32)
+        draws = self.lib.lrb_sample_pairs(self.h, n, count, pairs.ctypes.data)
+        if draws < 0:
+            raise LibrectifyError(_err(self.lib))
+        return pairs, int(draws)
+
+    # profiling -----------------------------------------------------------------------------------------------------------
+    def profile(self, on: bool = True):
+        self.lib.lrb_profile_enable(self.h, int(on))
+        self.lib.lrb_profile_reset(self.h)
+
+    def profile_read(self) -> dict:
+        ms = (C.c_double * len(TIMERS))()
+        g, k = C.c_longlong(0), C.c_longlong(0)
+        self.lib.lrb_profile_read(self.h, ms, C.byref(g), C.byref(k))
+        return dict(ms={name: ms[i] for i, name in enumerate(TIMERS)}, groups=g.value, kernels=k.value)

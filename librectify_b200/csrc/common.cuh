@@ -63,6 +63,7 @@ struct FrameCtrl {
     int line_overflow;
     int rounds_run;
     int flood_done;            // set by the serial fallback
+    int fit_done;              // components selected and fitted on final floods
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
     // grouping state
     int num_obs;               // reference estimator.h:119

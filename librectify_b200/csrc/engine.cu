@@ -1,0 +1,376 @@
+// engine.cu — host side of the B200 engine: workspace, TMA descriptors, launch sequence, read-back, fall-backs.
+//
+// One engine owns one CUDA stream and a workspace of `slots` frame slots; every kernel takes the slot as a grid
+// dimension, so a launch group pushes `slots` frames through the whole path
+//   ingest -> K1 grad5x5_bin -> K2 nms5x5_seeds -> K3 seed order -> K4 flood rounds -> K5 fit -> K6 filter+model
+//          -> 4 x (K7 sampler, K8 scoring grid, K9 refit/assign) -> read-back
+// with no host round-trip in between: all data-dependent sizes (seeds, components, segments, observations) live in a
+// per-slot control block on the device, kernels early-exit on it, and the host looks at it once per group.
+// Only when that single look shows unfinished floods (more speculative rounds needed, or an on-chip capacity was hit)
+// or an exhausted uniform stream does the host enqueue the missing work and look again.
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/librectify_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace lrb {
+void launch_sampler_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st);
+}
+
+using namespace lrb;
+
+namespace {
+
+thread_local std::string g_error;
+unsigned g_seed = 0;
+
+int fail(int code, const char * fmt, ...)
+{
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(-2, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void * p = nullptr; cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+// 3-D tensor map (x = column, y = row, z = frame) over a pitched plane set; out-of-range reads give zeros
+int make_tmap(CUtensorMap * m, CUtensorMapDataType dt, int esize, const void * base, int w, int h, int frames,
+              size_t pitch_elems, size_t frame_stride_elems, int box_w, int box_h)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(-3, "cuTensorMapEncodeTiled not available from the driver");
+    cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
+    cuuint64_t strides[2] = {(cuuint64_t)pitch_elems * esize, (cuuint64_t)frame_stride_elems * esize};
+    if (frames == 1 && (strides[1] == 0 || strides[1] % 16)) strides[1] = ((cuuint64_t)pitch_elems * esize * h + 15) / 16 * 16;
+    cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(m, dt, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(-3, "cuTensorMapEncodeTiled failed (%d) w=%d h=%d frames=%d pitch=%zu stride=%zu", (int)r, w, h, frames, pitch_elems, frame_stride_elems);
+    return 0;
+}
+
+constexpr int kT = kRansacIter;
+constexpr int kLinesHead = 4096;       // segments per slot copied back together with the control block
+constexpr int kInitialRounds = 8;
+
+} // namespace
+
+struct lrb_engine {
+    int device = 0, slots = 1;
+    cudaStream_t st = nullptr;
+    // workspace geometry
+    int w = 0, h = 0, pitch = 0;
+    size_t plane = 0;                  // elements per slot plane
+    void * arena = nullptr; size_t arena_bytes = 0;
+    Planes P{}; Seeds S{}; Comps K{}; Lines L{};
+    float * ws_img = nullptr;
+    FrameCtrl * ctrl = nullptr;        // device
+    FrameCtrl * h_ctrl = nullptr;      // pinned
+    SegRec * h_lines = nullptr;        // pinned, slots * kLinesHead
+    int * labels = nullptr;            // debug plane (lazily used)
+    CUtensorMap tm_img{}, tm_mag{}, tm_bin{};
+    unsigned next_epoch = 0xFE;
+    // uniform stream
+    unsigned * stream = nullptr; unsigned long long stream_len = 0; unsigned seed = 0;
+    // bookkeeping of the last group
+    int last_n = 0; std::vector<int> last_rounds, last_fallback;
+    // profiling
+    bool prof = false; cudaEvent_t ev[LRB_T_COUNT + 1] = {}; double ms[LRB_T_COUNT] = {}; long long groups = 0, kernels = 0;
+};
+
+namespace {
+
+template <class T> T * carve(char *& p, size_t n)
+{
+    T * r = reinterpret_cast<T *>(p);
+    p += (n * sizeof(T) + 255) / 256 * 256;
+    return r;
+}
+
+int ensure_stream(lrb_engine * e, unsigned long long need)
+{
+    if (e->stream && e->stream_len >= need && e->seed == g_seed) return 0;
+    unsigned long long len = std::max<unsigned long long>(need, e->seed == g_seed ? e->stream_len : 0);
+    if (e->stream) { CK(cudaStreamSynchronize(e->st)); CK(cudaFree(e->stream)); e->stream = nullptr; }
+    CK(cudaMalloc(&e->stream, len * sizeof(unsigned)));
+    e->stream_len = len; e->seed = g_seed;
+    launch_mt_stream(e->seed, e->stream, len, e->st);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// (re)allocate the workspace for frames of w x h
+int ensure_workspace(lrb_engine * e, int w, int h)
+{
+    if (e->arena && e->w == w && e->h == h) return 0;
+    if (w < 5 || h < 5 || w > 65535 || h > 65535) return fail(-1, "unsupported frame size %dx%d", w, h);
+    if (e->arena) { CK(cudaStreamSynchronize(e->st)); CK(cudaFree(e->arena)); e->arena = nullptr; }
+    const int G = e->slots;
+    const int pitch = (w + 15) / 16 * 16;
+    const size_t plane = (size_t)pitch * h;
+    const size_t npx = (size_t)w * h;
+    const int cap_seeds = (int)std::min<size_t>(npx / 8 + 1024, (1u << 24) - 1);
+    const int cap_comp = (int)(npx / 6 + 16);
+    const size_t cap_px = npx;
+    const int cap_lines = cap_comp;
+    auto layout = [&](char * base) {
+        char * p = base;
+        e->ws_img = carve<float>(p, plane * G);
+        e->P.dx = carve<float>(p, plane * G); e->P.dy = carve<float>(p, plane * G); e->P.mag = carve<float>(p, plane * G);
+        e->P.bin = carve<uint8_t>(p, plane * G); e->P.mask8 = carve<uint8_t>(p, plane * G);
+        e->P.owner = carve<unsigned>(p, plane * G);
+        e->S.us_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.us_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
+        e->S.b_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.b_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
+        e->S.idx = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.thr = carve<float>(p, (size_t)cap_seeds * G);
+        e->S.bin = carve<uint8_t>(p, (size_t)cap_seeds * G); e->S.status = carve<unsigned>(p, (size_t)cap_seeds * G);
+        e->S.fail_epoch = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.size = carve<int>(p, (size_t)cap_seeds * G);
+        e->S.hist = carve<int>(p, (size_t)kSeedBuckets * G); e->S.start = carve<int>(p, (size_t)kSeedBuckets * G);
+        e->S.cursor = carve<int>(p, (size_t)kSeedBuckets * G);
+        e->K.rank = carve<int>(p, (size_t)cap_comp * G); e->K.off = carve<int>(p, (size_t)cap_comp * G);
+        e->K.size = carve<int>(p, (size_t)cap_comp * G);
+        e->K.px = carve<unsigned>(p, cap_px * G); e->K.val = carve<float>(p, cap_px * G);
+        e->K.seg = carve<float>(p, (size_t)cap_comp * 7 * G);
+        e->L.seg = carve<float>(p, (size_t)cap_lines * 7 * G); e->L.h = carve<float>(p, (size_t)cap_lines * 3 * G);
+        e->L.anchor = carve<float>(p, (size_t)cap_lines * 2 * G); e->L.dir = carve<float>(p, (size_t)cap_lines * 2 * G);
+        e->L.len = carve<float>(p, (size_t)cap_lines * G);
+        e->L.inlier = carve<int>(p, (size_t)cap_lines * G); e->L.garbage = carve<int>(p, (size_t)cap_lines * G);
+        e->L.obs = carve<int>(p, (size_t)cap_lines * G); e->L.tmp = carve<int>(p, (size_t)cap_lines * G);
+        e->L.pairs = carve<int>(p, (size_t)2 * kT * G); e->L.scores = carve<float>(p, (size_t)kMaxModels * kT * G);
+        e->labels = carve<int>(p, npx);
+        e->ctrl = carve<FrameCtrl>(p, G);
+        return (size_t)(p - base);
+    };
+    const size_t bytes = layout(nullptr);
+    CK(cudaMalloc(&e->arena, bytes));
+    e->arena_bytes = bytes;
+    layout(static_cast<char *>(e->arena));
+    e->w = w; e->h = h; e->pitch = pitch; e->plane = plane;
+    e->P.w = w; e->P.h = h; e->P.pitch = pitch; e->P.stride = plane;
+    e->P.img = e->ws_img; e->P.img_stride = plane; e->P.img_pitch = pitch;
+    e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->L.cap = cap_lines;
+    CK(cudaMemsetAsync(e->arena, 0, bytes, e->st));
+    launch_fill_u32(e->P.owner, plane * G, kOwnerInit, e->st);
+    e->next_epoch = 0xFE;
+    int mw, mh, bw, bh; nms_tile_dims(&mw, &mh, &bw, &bh);
+    if (int r = make_tmap(&e->tm_img, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, e->ws_img, w, h, G, pitch, plane, grad_tile_w(), grad_tile_h())) return r;
+    if (int r = make_tmap(&e->tm_mag, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, e->P.mag, w, h, G, pitch, plane, mw, mh)) return r;
+    if (int r = make_tmap(&e->tm_bin, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, e->P.bin, w, h, G, pitch, plane, bw, bh)) return r;
+    if (!e->h_ctrl) { CK(cudaHostAlloc(&e->h_ctrl, sizeof(FrameCtrl) * G, cudaHostAllocDefault)); }
+    if (!e->h_lines) { CK(cudaHostAlloc(&e->h_lines, sizeof(SegRec) * kLinesHead * G, cudaHostAllocDefault)); }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+} // namespace
+
+// ---- one launch group ---------------------------------------------------------------------------------------------------
+namespace {
+
+struct Tick {
+    lrb_engine * e; int cur = -1;
+    explicit Tick(lrb_engine * e_) : e(e_) {}
+    void at(int stage) { if (e->prof) { cudaEventRecord(e->ev[stage], e->st); cur = stage; } }
+    void end() { if (e->prof) cudaEventRecord(e->ev[LRB_T_COUNT], e->st); }
+};
+
+void enqueue_tail(lrb_engine * e, int n, float min_length, int rounds_total, Tick & tk)
+{
+    tk.at(LRB_T_FIT);
+    launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds_total, e->st);
+    tk.at(LRB_T_MODEL);
+    launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds_total, e->st);
+    tk.at(LRB_T_RANSAC);
+    launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st);
+    e->kernels += 2 + 1 + 3 * kMaxModels + 1;
+}
+
+int readback(lrb_engine * e, int n, Tick & tk)
+{
+    tk.at(LRB_T_READBACK);
+    CK(cudaMemcpyAsync(e->h_ctrl, e->ctrl, sizeof(FrameCtrl) * n, cudaMemcpyDeviceToHost, e->st));
+    const int head = std::min(e->L.cap, kLinesHead);
+    CK(cudaMemcpy2DAsync(e->h_lines, sizeof(SegRec) * kLinesHead, e->L.seg, sizeof(SegRec) * (size_t)e->L.cap,
+                         sizeof(SegRec) * head, n, cudaMemcpyDeviceToHost, e->st));
+    tk.end();
+    CK(cudaStreamSynchronize(e->st));
+    return 0;
+}
+
+void collect_profile(lrb_engine * e, const std::vector<int> & order)
+{
+    if (!e->prof) return;
+    // order: the stages recorded, in stream order; each lasts until the next recorded event
+    for (size_t i = 0; i < order.size(); ++i) {
+        cudaEvent_t a = e->ev[order[i]], b = (i + 1 < order.size()) ? e->ev[order[i + 1]] : e->ev[LRB_T_COUNT];
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, a, b) == cudaSuccess) e->ms[order[i]] += ms;
+    }
+}
+
+int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w, int h, long long pitch,
+              long long fstride, float min_length)
+{
+    if (n < 1 || n > e->slots) return fail(-1, "group of %d frames does not fit %d slots", n, e->slots);
+    CK(cudaSetDevice(e->device));
+    if (int r = ensure_workspace(e, w, h)) return r;
+    // ~0.67 n draws per sample; start with room for n ~ 3000 over four solves and grow on demand
+    if (int r = ensure_stream(e, std::max<unsigned long long>(e->stream_len, 1ull << 25))) return r;
+    if (e->next_epoch < (unsigned)kMaxRounds + 4) {
+        launch_fill_u32(e->P.owner, e->plane * e->slots, kOwnerInit, e->st);
+        e->next_epoch = 0xFE; e->kernels++;
+    }
+    const unsigned epoch_first = e->next_epoch;
+    Tick tk(e);
+    std::vector<int> order;
+    auto stage = [&](int s) { tk.at(s); order.push_back(s); };
+
+    // ---- ingest (reference src/image.cpp:11-20: dense copy of a strided, possibly bottom-up buffer) ------------------
+    stage(LRB_T_INGEST);
+    CUtensorMap tm_user; const CUtensorMap * tm = &e->tm_img;
+    if (on_device) {
+        const bool direct = pitch > 0 && (reinterpret_cast<uintptr_t>(frames) % 16 == 0) && (pitch % 4 == 0) &&
+                            (n == 1 || (fstride > 0 && fstride % 4 == 0));
+        if (direct) {
+            if (int r = make_tmap(&tm_user, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, frames, w, h, n, (size_t)pitch,
+                                  (size_t)(n == 1 ? 0 : fstride), grad_tile_w(), grad_tile_h())) return r;
+            tm = &tm_user;
+        } else {
+            const float * base = frames; long long p = pitch;
+            if (p < 0) { base = frames + (long long)(h - 1) * p; p = -p; }
+            launch_ingest(base, p, fstride, e->ws_img, e->pitch, e->plane, w, h, n, e->st); e->kernels++;
+        }
+    } else {
+        for (int i = 0; i < n; ++i) {
+            const float * base = frames + (long long)i * fstride; long long p = pitch;
+            if (p < 0) { base = base + (long long)(h - 1) * p; p = -p; }
+            CK(cudaMemcpy2DAsync(e->ws_img + (size_t)i * e->plane, sizeof(float) * e->pitch, base, sizeof(float) * (size_t)p,
+                                 sizeof(float) * w, h, cudaMemcpyHostToDevice, e->st));
+        }
+    }
+    // ---- detection ---------------------------------------------------------------------------------------------------
+    stage(LRB_T_GRAD);
+    launch_frame_init(e->S, e->ctrl, n, e->st);
+    launch_grad(*tm, e->P, e->ctrl, n, e->st);
+    stage(LRB_T_NMS);
+    launch_nms(e->tm_mag, e->tm_bin, e->P, e->S, e->ctrl, n, e->st);
+    stage(LRB_T_SEEDS);
+    launch_seed_order(e->P, e->S, e->ctrl, n, e->S.cap, e->st);
+    stage(LRB_T_FLOOD);
+    int rounds = kInitialRounds;
+    launch_flood_rounds(e->P, e->S, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
+    e->kernels += 2 + 1 + 3 + 2 * rounds;
+    order.push_back(LRB_T_FIT); order.push_back(LRB_T_MODEL); order.push_back(LRB_T_RANSAC); order.push_back(LRB_T_READBACK);
+    enqueue_tail(e, n, min_length, rounds, tk);
+    if (int r = readback(e, n, tk)) return r;
+    CK(cudaGetLastError());
+    collect_profile(e, order);
+    e->groups++;
+
+    // ---- the single look at the control blocks; enqueue what is missing (rare) ---------------------------------------
+    e->last_fallback.assign(n, 0);
+    bool prof_saved = e->prof; e->prof = false;          // repair passes are not part of the per-stage profile
+    Tick quiet(e);
+    for (int guard = 0; guard < 64; ++guard) {
+        bool more_rounds = false, serial = false, more_stream = false;
+        for (int i = 0; i < n; ++i) {
+            const FrameCtrl & C = e->h_ctrl[i];
+            if (C.seed_overflow) { e->prof = prof_saved; return fail(-4, "frame %d: more than %d gradient peaks (seed capacity)", i, e->S.cap); }
+            if (C.comp_overflow || C.line_overflow) { e->prof = prof_saved; return fail(-4, "frame %d: component/segment capacity exceeded", i); }
+            if (C.flood_overflow) serial = true;
+            else if (!C.flood_done && C.live[rounds] != 0) more_rounds = true;
+            if (C.stream_overflow) more_stream = true;
+        }
+        if (!more_rounds && !serial && !more_stream) break;
+        if (more_rounds && !serial) {
+            if (rounds + 16 <= kMaxRounds) {
+                launch_flood_rounds(e->P, e->S, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
+                e->kernels += 32; rounds += 16;
+            } else serial = true;
+        }
+        if (serial) {
+            launch_flood_serial(e->P, e->S, e->K, e->ctrl, n, epoch_first, epoch_first - (unsigned)kMaxRounds - 1, e->st);
+            e->kernels++;
+            for (int i = 0; i < n; ++i) if (e->h_ctrl[i].flood_overflow || e->h_ctrl[i].live[rounds]) e->last_fallback[i] = 1;
+        }
+        if (more_stream) { if (int r = ensure_stream(e, e->stream_len * 2)) { e->prof = prof_saved; return r; } }
+        enqueue_tail(e, n, min_length, rounds, quiet);
+        if (int r = readback(e, n, quiet)) { e->prof = prof_saved; return r; }
+        CK(cudaGetLastError());
+    }
+    e->prof = prof_saved;
+    e->next_epoch = epoch_first - (unsigned)rounds - 2;
+    if (std::any_of(e->last_fallback.begin(), e->last_fallback.end(), [](int v) { return v != 0; })) e->next_epoch = 0;   // force a re-init
+    e->last_n = n;
+    e->last_rounds.assign(n, 0);
+    for (int i = 0; i < n; ++i) e->last_rounds[i] = e->h_ctrl[i].rounds_run;
+    return 0;
+}
+
+void fill_info(const lrb_engine * e, int i, lrb_frame_info * out)
+{
+    const FrameCtrl & C = e->h_ctrl[i];
+    out->n_lines = C.n_lines; out->n_seeds = C.n_seeds; out->n_components = C.n_comp; out->n_pixels = C.n_px;
+    out->flood_rounds = C.rounds_run; out->flood_fallback = e->last_fallback[i]; out->n_solves = C.n_solves;
+    for (int k = 0; k < 4; ++k) out->n_obs[k] = k < C.n_solves ? C.n_obs[k] : 0;
+    unsigned g = C.gmax_bits; float f; memcpy(&f, &g, 4); out->max_magnitude = f;
+}
+
+int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, int w, int h, long long pitch,
+           long long fstride, float min_length, lrb_frame_info * info, lrb_segment * lines, int lines_cap,
+           const lrb_config * cfg, int n_cfg, lrb_transform * tf)
+{
+    if (!e) return fail(-1, "null engine");
+    if (n_frames < 0 || !frames) return fail(-1, "bad arguments");
+    if (pitch < 0 && n_frames != 1) return fail(-1, "negative pitch is only supported for a single frame");
+    std::vector<lrb_segment> tmp;
+    for (int f0 = 0; f0 < n_frames; f0 += e->slots) {
+        const int n = std::min(e->slots, n_frames - f0);
+        if (int r = run_group(e, frames + (long long)f0 * fstride, on_device, n, w, h, pitch, fstride, min_length)) return r;
+        for (int i = 0; i < n; ++i) {
+            const int nl = e->h_ctrl[i].n_lines;
+            if (info) fill_info(e, i, &info[f0 + i]);
+            const lrb_segment * src = reinterpret_cast<const lrb_segment *>(e->h_lines) + (size_t)i * kLinesHead;
+            const int want = tf ? nl : std::min(nl, lines ? lines_cap : 0);
+            if (want > kLinesHead) {                       // long tail: fetch the rest of this frame's segments
+                tmp.resize(want);
+                CK(cudaMemcpy(tmp.data(), e->L.seg + (size_t)i * e->L.cap * 7, sizeof(lrb_segment) * want, cudaMemcpyDeviceToHost));
+                src = tmp.data();
+            }
+            if (lines && lines_cap > 0) memcpy(lines + (size_t)(f0 + i) * lines_cap, src, sizeof(lrb_segment) * std::min(nl, lines_cap));
+            if (tf) lrb_compute_transform(src, nl, w, h, &cfg[(f0 + i) % n_cfg], &tf[f0 + i]);
+        }
+    }
+    return 0;
+}
+
+} // namespace
+
+#include "engine_api.inc"

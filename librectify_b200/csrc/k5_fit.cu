@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(1024) k_comp_select(Seeds S, Comps K, FrameCtr
     const int n = C.n_seeds;
     const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (C.fit_done) return;                               // repair pass for another slot: this one is already fitted
     // floods not finished (more rounds or the serial fallback needed): publish nothing; the host re-runs from here
     if ((C.live[rounds_total] != 0 && !C.flood_done) || C.flood_overflow) {
         if (t == 0) { C.n_comp = 0; C.n_px = 0; }
@@ -103,6 +104,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
     __shared__ float stage_all[FIT_WARPS][3][32];
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
+    if (C.fit_done) return;
     const int ncomp = C.n_comp;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float (*stage)[32] = stage_all[warp];

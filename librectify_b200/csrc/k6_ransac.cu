@@ -90,9 +90,16 @@ __global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCt
     const int ncomp = C.n_comp;
     SegRec * seg = reinterpret_cast<SegRec *>(L.seg) + lo;
     const SegRec * raw = reinterpret_cast<const SegRec *>(K.seg) + ko;
-    if (t == 0) s_base = 0;
+    const bool floods_complete = (C.live[rounds_total] == 0 || C.flood_done) && !C.flood_overflow;
+    if (t == 0) {
+        s_base = 0;
+        // (re)start the grouping state: this kernel is also the entry point of a repair pass
+        for (int k = 0; k < kMaxModels; ++k) { C.best[k] = 0ull; C.winner[k] = -1; C.n_obs[k] = 0; }
+        C.stream_pos = 0ull; C.stream_overflow = 0; C.n_solves = 0;
+        if (floods_complete) C.fit_done = 1;             // the fit kernels ran on final floods: never redo them (they consume the owner stamps)
+    }
     __syncthreads();
-    if (ncomp < 2) {                                                            // interface.cpp:50-54
+    if (ncomp < 2 || !floods_complete) {                                                            // interface.cpp:50-54
         if (t == 0) { C.n_lines = 0; C.num_obs = 0; }
         return;
     }
@@ -383,6 +390,11 @@ __global__ void k_finalize(Lines L, FrameCtrl * ctrl)
 void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, cudaStream_t st)
 {
     k_filter_model<<<n_slots, 1024, 0, st>>>(K, L, ctrl, min_length, rounds_total);
+}
+
+void launch_sampler_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st)
+{
+    k_sampler<<<1, 32, 0, st>>>(L, ctrl, stream, stream_len, 0, T);
 }
 
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
