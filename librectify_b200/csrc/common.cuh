@@ -82,6 +82,8 @@ struct FrameCtrl {
 // ---- views passed to kernels by value -----------------------------------------------------------------------------
 struct Planes {                 // one frame slot = one set of planes; slot s lives at base + s * stride
     int w, h, pitch;            // pitch in elements, multiple of 16 (TMA needs 16-byte row strides, also for the byte planes)
+    int wq;                     // w rounded up to 4: columns written by the 4-wide vector stores
+    // plane pointers address pixel (0,0); an optional zero margin (kMarginX / kMarginY, currently 0) may precede it
     size_t stride;              // elements per slot plane (pitch * h rounded up)
     const float * img;          // input frames (may alias user memory): img + s * img_stride + r * img_pitch + c
     size_t img_stride; int img_pitch;
@@ -126,6 +128,8 @@ struct Lines {                  // per slot: filtered segments and the pencil mo
     int * pairs;                // 2 x T per slot: sampled positions in the observation list
     float * scores;             // kMaxModels x T per slot (-1 = rejected by sample_check); kept for the parity tests
 };
+
+constexpr int kMarginX = 0, kMarginY = 0;    // no margin needed: TMA accepts negative box origins (they only have to be 16-byte aligned in x)
 
 constexpr unsigned kStatusLive = 0u, kStatusDropped = 1u;
 constexpr unsigned kOwnerInit = 0xFFFFFFFFu;          // epoch field 0xFF: never visited, loses every atomicMin

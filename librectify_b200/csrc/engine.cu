@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -91,7 +92,8 @@ struct lrb_engine {
     size_t plane = 0;                  // elements per slot plane
     void * arena = nullptr; size_t arena_bytes = 0;
     Planes P{}; Seeds S{}; Comps K{}; Lines L{};
-    float * ws_img = nullptr;
+    float * ws_img = nullptr;          // pixel (0,0) of slot 0 of the workspace image (inside the zero margin)
+    float * ws_img_raw = nullptr; unsigned * owner_raw = nullptr;
     FrameCtrl * ctrl = nullptr;        // device
     FrameCtrl * h_ctrl = nullptr;      // pinned
     SegRec * h_lines = nullptr;        // pinned, slots * kLinesHead
@@ -134,8 +136,9 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     if (w < 5 || h < 5 || w > 65535 || h > 65535) return fail(-1, "unsupported frame size %dx%d", w, h);
     if (e->arena) { CK(cudaStreamSynchronize(e->st)); CK(cudaFree(e->arena)); e->arena = nullptr; }
     const int G = e->slots;
-    const int pitch = (w + 15) / 16 * 16;
-    const size_t plane = (size_t)pitch * h;
+    const int pitch = kMarginX + (w + 15) / 16 * 16;
+    const size_t plane = (size_t)pitch * (h + kMarginY);
+    const size_t org = (size_t)kMarginY * pitch + kMarginX;
     const size_t npx = (size_t)w * h;
     const int cap_seeds = (int)std::min<size_t>(npx / 8 + 1024, (1u << 24) - 1);
     const int cap_comp = (int)(npx / 6 + 16);
@@ -143,10 +146,10 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     const int cap_lines = cap_comp;
     auto layout = [&](char * base) {
         char * p = base;
-        e->ws_img = carve<float>(p, plane * G);
-        e->P.dx = carve<float>(p, plane * G); e->P.dy = carve<float>(p, plane * G); e->P.mag = carve<float>(p, plane * G);
-        e->P.bin = carve<uint8_t>(p, plane * G); e->P.mask8 = carve<uint8_t>(p, plane * G);
-        e->P.owner = carve<unsigned>(p, plane * G);
+        e->ws_img_raw = carve<float>(p, plane * G); e->ws_img = e->ws_img_raw + org;
+        e->P.dx = carve<float>(p, plane * G) + org; e->P.dy = carve<float>(p, plane * G) + org; e->P.mag = carve<float>(p, plane * G) + org;
+        e->P.bin = carve<uint8_t>(p, plane * G) + org; e->P.mask8 = carve<uint8_t>(p, plane * G) + org;
+        e->owner_raw = carve<unsigned>(p, plane * G); e->P.owner = e->owner_raw + org;
         e->S.us_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.us_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.b_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.b_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.idx = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.thr = carve<float>(p, (size_t)cap_seeds * G);
@@ -173,16 +176,17 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     e->arena_bytes = bytes;
     layout(static_cast<char *>(e->arena));
     e->w = w; e->h = h; e->pitch = pitch; e->plane = plane;
-    e->P.w = w; e->P.h = h; e->P.pitch = pitch; e->P.stride = plane;
+    e->P.w = w; e->P.h = h; e->P.pitch = pitch; e->P.stride = plane; e->P.wq = (w + 3) / 4 * 4;
     e->P.img = e->ws_img; e->P.img_stride = plane; e->P.img_pitch = pitch;
     e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->L.cap = cap_lines;
     CK(cudaMemsetAsync(e->arena, 0, bytes, e->st));
-    launch_fill_u32(e->P.owner, plane * G, kOwnerInit, e->st);
+    launch_fill_u32(e->owner_raw, plane * G, kOwnerInit, e->st);
     e->next_epoch = 0xFE;
     int mw, mh, bw, bh; nms_tile_dims(&mw, &mh, &bw, &bh);
-    if (int r = make_tmap(&e->tm_img, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, e->ws_img, w, h, G, pitch, plane, grad_tile_w(), grad_tile_h())) return r;
-    if (int r = make_tmap(&e->tm_mag, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, e->P.mag, w, h, G, pitch, plane, mw, mh)) return r;
-    if (int r = make_tmap(&e->tm_bin, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, e->P.bin, w, h, G, pitch, plane, bw, bh)) return r;
+    const int tw = kMarginX + w, th = kMarginY + h;      // tensor extents: margin + image; everything beyond reads as zero
+    if (int r = make_tmap(&e->tm_img, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, e->ws_img_raw, tw, th, G, pitch, plane, grad_tile_w(), grad_tile_h())) return r;
+    if (int r = make_tmap(&e->tm_mag, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, e->P.mag - org, tw, th, G, pitch, plane, mw, mh)) return r;
+    if (int r = make_tmap(&e->tm_bin, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, e->P.bin - org, tw, th, G, pitch, plane, bw, bh)) return r;
     if (!e->h_ctrl) { CK(cudaHostAlloc(&e->h_ctrl, sizeof(FrameCtrl) * G, cudaHostAllocDefault)); }
     if (!e->h_lines) { CK(cudaHostAlloc(&e->h_lines, sizeof(SegRec) * kLinesHead * G, cudaHostAllocDefault)); }
     CK(cudaGetLastError());
@@ -244,24 +248,36 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     // ~0.67 n draws per sample; start with room for n ~ 3000 over four solves and grow on demand
     if (int r = ensure_stream(e, std::max<unsigned long long>(e->stream_len, 1ull << 25))) return r;
     if (e->next_epoch < (unsigned)kMaxRounds + 4) {
-        launch_fill_u32(e->P.owner, e->plane * e->slots, kOwnerInit, e->st);
+        launch_fill_u32(e->owner_raw, e->plane * e->slots, kOwnerInit, e->st);
         e->next_epoch = 0xFE; e->kernels++;
     }
     const unsigned epoch_first = e->next_epoch;
     Tick tk(e);
     std::vector<int> order;
-    auto stage = [&](int s) { tk.at(s); order.push_back(s); };
+    static const bool debug_sync = getenv("LRB_DEBUG_SYNC") != nullptr;      // fault isolation: sync after every stage
+    static const char * stage_names[] = {"ingest", "grad", "nms", "seeds", "flood", "fit", "model", "ransac", "readback"};
+    int prev_stage = -1; cudaError_t stage_err = cudaSuccess;
+    auto stage = [&](int s) {
+        if (debug_sync && prev_stage >= 0 && stage_err == cudaSuccess) {
+            stage_err = cudaStreamSynchronize(e->st);
+            if (stage_err != cudaSuccess) fprintf(stderr, "[lrb] stage '%s' failed: %s\n", stage_names[prev_stage], cudaGetErrorString(stage_err));
+        }
+        prev_stage = s;
+        tk.at(s); order.push_back(s);
+    };
 
     // ---- ingest (reference src/image.cpp:11-20: dense copy of a strided, possibly bottom-up buffer) ------------------
     stage(LRB_T_INGEST);
     CUtensorMap tm_user; const CUtensorMap * tm = &e->tm_img;
+    Planes P1 = e->P; int tma_x = kMarginX, tma_y = kMarginY;      // K1's view: where the input image lives
     if (on_device) {
         const bool direct = pitch > 0 && (reinterpret_cast<uintptr_t>(frames) % 16 == 0) && (pitch % 4 == 0) &&
                             (n == 1 || (fstride > 0 && fstride % 4 == 0));
         if (direct) {
             if (int r = make_tmap(&tm_user, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, frames, w, h, n, (size_t)pitch,
                                   (size_t)(n == 1 ? 0 : fstride), grad_tile_w(), grad_tile_h())) return r;
-            tm = &tm_user;
+            tm = &tm_user; tma_x = tma_y = 0;
+            P1.img = frames; P1.img_pitch = (int)pitch; P1.img_stride = (size_t)(n == 1 ? 0 : fstride);
         } else {
             const float * base = frames; long long p = pitch;
             if (p < 0) { base = frames + (long long)(h - 1) * p; p = -p; }
@@ -278,17 +294,25 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     // ---- detection ---------------------------------------------------------------------------------------------------
     stage(LRB_T_GRAD);
     launch_frame_init(e->S, e->ctrl, n, e->st);
-    launch_grad(*tm, e->P, e->ctrl, n, e->st);
+    launch_grad(*tm, P1, e->ctrl, n, tma_x, tma_y, e->st);
     stage(LRB_T_NMS);
-    launch_nms(e->tm_mag, e->tm_bin, e->P, e->S, e->ctrl, n, e->st);
+    launch_nms(e->tm_mag, e->tm_bin, e->P, e->S, e->ctrl, n, kMarginX, kMarginY, e->st);
     stage(LRB_T_SEEDS);
     launch_seed_order(e->P, e->S, e->ctrl, n, e->S.cap, e->st);
     stage(LRB_T_FLOOD);
     int rounds = kInitialRounds;
     launch_flood_rounds(e->P, e->S, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
     e->kernels += 2 + 1 + 3 + 2 * rounds;
+    if (debug_sync) {
+        stage(LRB_T_FIT); launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds, e->st);
+        stage(LRB_T_MODEL); launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds, e->st);
+        stage(LRB_T_RANSAC); launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st);
+        stage(LRB_T_READBACK);
+        order.resize(order.size() - 4);
+        if (stage_err != cudaSuccess) return fail(-2, "debug sync: a stage failed (see stderr): %s", cudaGetErrorString(stage_err));
+    }
     order.push_back(LRB_T_FIT); order.push_back(LRB_T_MODEL); order.push_back(LRB_T_RANSAC); order.push_back(LRB_T_READBACK);
-    enqueue_tail(e, n, min_length, rounds, tk);
+    if (!debug_sync) enqueue_tail(e, n, min_length, rounds, tk);
     if (int r = readback(e, n, tk)) return r;
     CK(cudaGetLastError());
     collect_profile(e, order);

@@ -14,7 +14,7 @@
 //   Zero taps contribute x*0 = +-0, which can only change the sign of an exactly-zero sum when the input holds
 //   negative zeros; they are skipped ("K1 exactness").
 //
-// Data movement: a (128+4) x (8*RPT+4) halo tile is staged into shared memory by ONE cp.async.bulk.tensor (TMA) per
+// Data movement: a (4+128+4) x (8*RPT+4) halo tile is staged into shared memory by ONE cp.async.bulk.tensor (TMA) per
 // CTA; the copy engine zero-fills outside the image.  Each thread owns a 4-column x RPT-row strip, slides down the
 // tile keeping five partially accumulated output rows in registers, and writes dx/dy/mag as 128-bit and bin as
 // 32-bit coalesced stores.  HBM traffic is the compulsory 4 B read + 13 B written per pixel.
@@ -27,7 +27,8 @@ namespace lrb {
 namespace {
 
 constexpr int K1_TW = 128;          // tile width  (32 lanes x 4 columns)
-constexpr int K1_SW = K1_TW + 4;    // staged width incl. 2-px halo (528 B rows: multiple of 16 B as TMA requires)
+constexpr int K1_HALO_L = 4;        // staged columns left of the tile: 2 needed, 4 keeps the TMA box origin 16-byte aligned
+constexpr int K1_SW = K1_HALO_L + K1_TW + 4;   // staged width (544 B rows: multiple of 16 B as TMA requires)
 
 __device__ __forceinline__ void finish_pixel(float dx, float dy, bool valid, float & odx, float & ody, float & omag, unsigned & obin)
 {
@@ -58,7 +59,7 @@ __device__ __forceinline__ void finish_pixel(float dx, float dy, bool valid, flo
 
 template <int RPT>
 __global__ void __launch_bounds__(256)
-k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ctrl)
+k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ctrl, int tma_x, int tma_y)
 {
     constexpr int TH = 8 * RPT, SH = TH + 4;
     __shared__ __align__(128) float tile[SH * K1_SW];
@@ -69,11 +70,14 @@ k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ct
     const int x0 = blockIdx.x * K1_TW, y0 = blockIdx.y * TH;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+    // TMA requires the box origin to be 16-byte aligned along x (an unaligned start raises "illegal instruction" on
+    // B200), so the staged tile starts 4 columns (not 2) left of the first output column; negative / out-of-range
+    // coordinates are legal and zero-filled, which is the reference's border rule.
     if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_arrive_expect_tx(&bar, SH * K1_SW * sizeof(float));
-        tma_load_3d(tile, &tmap, x0 - 2, y0 - 2, slot, &bar);
+        tma_load_3d(tile, &tmap, x0 - K1_HALO_L + tma_x, y0 - 2 + tma_y, slot, &bar);
     }
     mbar_wait(&bar, 0);
 
@@ -87,9 +91,11 @@ k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ct
 
 #pragma unroll
     for (int i = 0; i < RPT + 4; ++i) {
-        const float4 lo = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4]);
-        const float4 hi = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4 + 4]);
-        const float p[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+        // staged column k <-> image column x0 - 4 + k; this thread needs image columns xq-2 .. xq+5 = staged 4*lane+2 .. +9
+        const float4 q0 = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4]);
+        const float4 q1 = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4 + 4]);
+        const float4 q2 = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4 + 8]);
+        const float p[8] = {q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y};
         float m[3][2][8];                       // m[a'][b'][j] = p[j] * |Hx(a',b')|
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -135,7 +141,7 @@ k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ct
         if (i >= 4) {
             const int j = i - 4;
             const int y = y0 + ty0 + j;
-            if (y < P.h && xq < P.pitch) {
+            if (y < P.h && xq < P.wq) {
                 const bool vy = (y >= 2) && (y < P.h - 2);
                 float4 odx, ody, omag; unsigned b0, b1, b2, b3;
                 finish_pixel(ax[j][0], ay[j][0], vy && (xq + 0 >= 2) && (xq + 0 < P.w - 2), odx.x, ody.x, omag.x, b0);
@@ -168,11 +174,11 @@ k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ct
 
 } // namespace
 
-void launch_grad(const CUtensorMap & tmap, const Planes & P, FrameCtrl * ctrl, int n_slots, cudaStream_t st)
+void launch_grad(const CUtensorMap & tmap, const Planes & P, FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st)
 {
     constexpr int RPT = 8;
     dim3 grid((P.w + K1_TW - 1) / K1_TW, (P.h + 8 * RPT - 1) / (8 * RPT), n_slots);
-    k_grad5x5_bin<RPT><<<grid, 256, 0, st>>>(tmap, P, ctrl);
+    k_grad5x5_bin<RPT><<<grid, 256, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
 }
 
 int grad_tile_w() { return K1_SW; }

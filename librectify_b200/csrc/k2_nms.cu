@@ -25,8 +25,9 @@ namespace lrb {
 namespace {
 
 constexpr int K2_TW = 128, K2_TH = 32;
-constexpr int K2_MW = K2_TW + 4, K2_MH = K2_TH + 4;        // mag tile, 2-px halo
-constexpr int K2_BW = 144, K2_BH = K2_TH + 2;              // bin tile, 1-px halo (130 B needed; 144 = next multiple of 16)
+// TMA box origins must be 16-byte aligned along x: the mag tile starts 4 floats, the bin tile 16 bytes left of the tile
+constexpr int K2_MW = 4 + K2_TW + 4, K2_MH = K2_TH + 4;    // mag tile: columns x0-4 .. x0+131, rows y0-2 .. y0+33
+constexpr int K2_BW = 160, K2_BH = K2_TH + 2;              // bin tile: columns x0-16 .. x0+143, rows y0-1 .. y0+32
 
 // monotone (non-decreasing in mag) bucket index, then flipped so that bucket 0 holds the largest magnitudes
 __device__ __forceinline__ int seed_bucket(float mag, float thr, float gmax)
@@ -39,7 +40,7 @@ __device__ __forceinline__ int seed_bucket(float mag, float thr, float gmax)
 
 __global__ void __launch_bounds__(256)
 k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
-               Planes P, Seeds S, FrameCtrl * ctrl)
+               Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y)
 {
     __shared__ __align__(128) float tmag[K2_MH * K2_MW];
     __shared__ __align__(128) uint8_t tbin[K2_BH * K2_BW];
@@ -53,8 +54,8 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_arrive_expect_tx(&bar, K2_MH * K2_MW * 4 + K2_BH * K2_BW);
-        tma_load_3d(tmag, &tmap_mag, x0 - 2, y0 - 2, slot, &bar);
-        tma_load_3d(tbin, &tmap_bin, x0 - 1, y0 - 1, slot, &bar);
+        tma_load_3d(tmag, &tmap_mag, x0 - 4 + tma_x, y0 - 2 + tma_y, slot, &bar);
+        tma_load_3d(tbin, &tmap_bin, x0 - 16 + tma_x, y0 - 1 + tma_y, slot, &bar);
     }
     const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
     const float thr = __fmul_rn(gmax, kSeedFactor);
@@ -67,9 +68,10 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
     float hm[8][4], ctr[4][4];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        const float4 lo = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4]);
-        const float4 hi = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4 + 4]);
-        const float p[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+        const float4 q0 = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4]);
+        const float4 q1 = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4 + 4]);
+        const float4 q2 = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4 + 8]);
+        const float p[8] = {q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y};      // image columns xq-2 .. xq+5
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             hm[i][c] = fmaxf(fmaxf(fmaxf(p[c], p[c + 1]), fmaxf(p[c + 2], p[c + 3])), p[c + 4]);
@@ -91,16 +93,18 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
     }
 
     // ---- 3x3 dilation of the one-hot bin masks ---------------------------------------------------------------------
-    // tbin row i <-> image row y0-1+i, byte k <-> image column x0-1+k; this thread needs columns xq-1 .. xq+4
+    // tbin row i <-> image row y0-1+i, byte k <-> image column x0-16+k; this thread needs columns xq-1 .. xq+4 = bytes 4*lane+15 .. +20
     unsigned hor[6];                            // per staged row: 4 bytes, byte c = OR of one-hot(bin) over columns c-1..c+1
 #pragma unroll
     for (int i = 0; i < 6; ++i) {
-        const unsigned w0 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4]);
-        const unsigned w1 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 4]);
+        const unsigned w0 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 12]);
+        const unsigned w1 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 16]);
+        const unsigned w2 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 20]);
         unsigned oh[6];
+        oh[0] = 1u << ((w0 >> 24) & 7u);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) oh[k] = 1u << ((w0 >> (8 * k)) & 7u);
-        oh[4] = 1u << (w1 & 7u); oh[5] = 1u << ((w1 >> 8) & 7u);
+        for (int k = 0; k < 4; ++k) oh[k + 1] = 1u << ((w1 >> (8 * k)) & 7u);
+        oh[5] = 1u << (w2 & 7u);
         // out-of-image staged bytes are 0 (bin 0); they are only ever combined into border pixels, which are forced to 0
         hor[i] = (oh[0] | oh[1] | oh[2]) | ((oh[1] | oh[2] | oh[3]) << 8) | ((oh[2] | oh[3] | oh[4]) << 16) | ((oh[3] | oh[4] | oh[5]) << 24);
     }
@@ -108,7 +112,7 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const int y = y0 + ty0 + j;
-        if (y < P.h && xq < P.pitch) {
+        if (y < P.h && xq < P.wq) {
             unsigned mword = hor[j] | hor[j + 1] | hor[j + 2];
             const bool vy = (y >= 1) && (y < P.h - 1);
             unsigned keep = 0;
@@ -244,10 +248,10 @@ void launch_frame_init(const Seeds & S, FrameCtrl * ctrl, int n_slots, cudaStrea
 }
 
 void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, const Planes & P, const Seeds & S,
-                FrameCtrl * ctrl, int n_slots, cudaStream_t st)
+                FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st)
 {
     dim3 grid((P.w + K2_TW - 1) / K2_TW, (P.h + K2_TH - 1) / K2_TH, n_slots);
-    k_nms5x5_seeds<<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl);
+    k_nms5x5_seeds<<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
 }
 
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st)

@@ -23,8 +23,7 @@ namespace lrb {
 namespace {
 
 constexpr int FL_WARPS = 8;
-constexpr int FL_QCAP  = 512;     // BFS ring per warp (frontier, not region, bounds it)
-constexpr int FL_LCAP  = 96;      // pixels reached but owned by a higher-priority seed (needed only for termination)
+constexpr int FL_QCAP  = 1024;    // BFS ring per warp: must hold three consecutive BFS levels (frontier-, not region-bound)
 
 // reference src/filter.cpp:113-116 neighbour order (dr, dc)
 static __device__ __constant__ const int kDr[8] = {0, 0, 1, -1, -1, -1, 1, 1};
@@ -37,8 +36,14 @@ __device__ __forceinline__ bool is_visited(unsigned o, unsigned epoch_first, con
 }
 
 // one tentative flood of seed `rank` by one warp
+//
+// The warp runs a level-synchronous BFS over the seed's tentative region: each step expands up to four pixels of the
+// current level against their eight neighbours (32 candidates, one per lane).  The ring `q` keeps every pixel pushed
+// for the previous, the current and the next level.  A pixel this seed stamped is recognised by owner == key; a pixel
+// stamped by a higher-priority seed (it stays part of the tentative region and is explored through) cannot be, so it
+// is looked up in that three-level window instead — a neighbour of a level-L pixel always lies in level L-1, L or L+1.
 __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, FrameCtrl & C, int slot, int rank,
-                                          unsigned epoch, unsigned epoch_first, unsigned * q, unsigned * lost)
+                                          unsigned epoch, unsigned epoch_first, unsigned * q)
 {
     const int lane = threadIdx.x & 31;
     const size_t so = (size_t)slot * S.cap;
@@ -52,39 +57,41 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, Fra
     const unsigned key = (epoch << 24) | (unsigned)rank;
     const unsigned spx = S.idx[so + rank];
     const int sr = spx / P.w, sc = spx - sr * P.w;
-    {
-        const unsigned o = __ldcg(owner + (size_t)sr * P.pitch + sc);
-        if (is_visited(o, epoch_first, status)) {              // line_detector.cpp:103: seed already swallowed
-            if (lane == 0) status[rank] = kStatusDropped;
-            return;
-        }
+    const size_t spo = (size_t)sr * P.pitch + sc;
+    if (is_visited(__ldcg(owner + spo), epoch_first, status)) {    // line_detector.cpp:103: seed already swallowed
+        if (lane == 0) status[rank] = kStatusDropped;
+        return;
     }
     const int b = S.bin[so + rank];
     const float thr = S.thr[so + rank];
     const float sb = kSin[b], cb = kCos[b];
 
-    int head = 0, tail = 0, nlost = 0, size = 0;
-    bool failed = false, overflow = false, first = true;
-
-    while (true) {
-        int cnt;
-        bool act;
-        int r, c;
-        if (first) {                                           // the seed itself: G_b(seed) > 0.75 G_b(seed) holds by construction
-            cnt = 1; act = (lane == 0); r = sr; c = sc;
-        } else {
-            cnt = min(4, tail - head);
-            if (cnt == 0) break;
-            const int pslot = lane >> 3, k = lane & 7;
-            act = pslot < cnt;
-            const unsigned prc = q[(head + (act ? pslot : 0)) & (FL_QCAP - 1)];
-            head += cnt;
-            r = (int)(prc >> 16) + kDr[k]; c = (int)(prc & 0xFFFFu) + kDc[k];
+    // the seed itself: G_b(seed) > 0.75 G_b(seed) holds by construction (filter.cpp:119-131)
+    bool failed = false, overflow = false;
+    if (lane == 0) {
+        const unsigned old = atomicMin(owner + spo, key);
+        if (owner_epoch(old) == epoch) {
+            if (old < key) failed = true;                                   // a higher-priority seed already reached this pixel
+            else if (old != key) S.fail_epoch[so + owner_rank(old)] = epoch;
         }
+        q[0] = ((unsigned)sr << 16) | (unsigned)sc;
+    }
+    __syncwarp();
+    int head = 0, tail = 1;                 // absolute positions in the push sequence; ring index = pos & (FL_QCAP-1)
+    int s_prev = 0, s_cur = 0, s_next = 1;  // first push of the previous / current / next BFS level
+
+    while (head < tail) {
+        if (head >= s_next) { s_prev = s_cur; s_cur = s_next; s_next = tail; }
+        const int cnt = min(4, s_next - head);                             // a step never straddles two levels
+        const int pslot = lane >> 3, k = lane & 7;
+        const bool act = pslot < cnt;
+        const unsigned prc = q[(head + (act ? pslot : 0)) & (FL_QCAP - 1)];
+        head += cnt;
+        const int r = (int)(prc >> 16) + kDr[k], c = (int)(prc & 0xFFFFu) + kDc[k];
         bool elig = act && r >= 1 && r < P.h - 1 && c >= 1 && c < P.w - 1;      // filter.cpp:101-107: border is visited
         const size_t po = (size_t)(elig ? r : 0) * P.pitch + (elig ? c : 0);
-        if (elig && !first) elig = (__ldg(mask8 + po) >> b) & 1;                // dilated bin mask, else G_b = 0
-        if (elig && !first) {
+        if (elig) elig = (__ldg(mask8 + po) >> b) & 1;                          // dilated bin mask, else G_b = 0
+        if (elig) {
             const float g = fabsf(__fadd_rn(__fmul_rn(__ldg(dx + po), sb), __fmul_rn(__ldg(dy + po), cb)));
             elig = g > thr;                                                     // filter.cpp:131
         }
@@ -111,27 +118,17 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, Fra
                 } else reached = true;
             }
         }
-        if (lostcand) {
+        if (lostcand) {                                                         // not ours: was it pushed in the last three levels?
             failed = true;
             bool seen = false;
-            for (int i = 0; i < nlost; ++i) seen |= (lost[i] == rcq);
-            lostcand = !seen;
-        }
-        const unsigned lm = __ballot_sync(0xffffffffu, lostcand);
-        if (lm) {
-            const int nl = __popc(lm);
-            if (nlost + nl > FL_LCAP) overflow = true;
-            else if (lostcand) lost[nlost + __popc(lm & ((1u << lane) - 1))] = rcq;
-            nlost += nl;
-            reached |= lostcand;                                                // still part of the tentative region: explore through it
+            for (int i = s_prev; i < tail; ++i) seen |= (q[i & (FL_QCAP - 1)] == rcq);
+            reached = !seen;                                                    // still part of the tentative region: explore through it
         }
         const unsigned pm = __ballot_sync(0xffffffffu, reached);
         const int np = __popc(pm);
-        if (tail + np - head > FL_QCAP) overflow = true;
-        if (__any_sync(0xffffffffu, overflow)) { overflow = true; break; }
+        if (tail + np - s_prev > FL_QCAP) { overflow = true; break; }           // the ring must keep three levels
         if (reached) q[(tail + __popc(pm & ((1u << lane) - 1))) & (FL_QCAP - 1)] = rcq;
-        tail += np; size += np;
-        first = false;
+        tail += np;
         __syncwarp();
     }
 
@@ -140,7 +137,7 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, Fra
         if (overflow) { C.flood_overflow = 1; S.fail_epoch[so + rank] = epoch; }
         else {
             if (failed) S.fail_epoch[so + rank] = epoch;
-            S.size[so + rank] = size;
+            S.size[so + rank] = tail;
         }
     }
     __syncwarp();
@@ -151,7 +148,6 @@ __global__ void __launch_bounds__(FL_WARPS * 32)
 k_flood_round(Planes P, Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_first)
 {
     __shared__ unsigned q[FL_WARPS][FL_QCAP];
-    __shared__ unsigned lost[FL_WARPS][FL_LCAP];
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
@@ -159,7 +155,7 @@ k_flood_round(Planes P, Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_fir
     const int warp = threadIdx.x >> 5;
     const unsigned epoch = epoch_first - (unsigned)round;
     for (int rank = blockIdx.x * FL_WARPS + warp; rank < n; rank += gridDim.x * FL_WARPS)
-        flood_one(P, S, C, slot, rank, epoch, epoch_first, q[warp], lost[warp]);
+        flood_one(P, S, C, slot, rank, epoch, epoch_first, q[warp]);
 }
 
 // commit every live seed that nobody out-prioritised in this round; count what is still live

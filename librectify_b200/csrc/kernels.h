@@ -7,13 +7,13 @@
 namespace lrb {
 
 // k1_grad.cu
-void launch_grad(const CUtensorMap & tmap_img, const Planes & P, FrameCtrl * ctrl, int n_slots, cudaStream_t st);
+void launch_grad(const CUtensorMap & tmap_img, const Planes & P, FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st);
 int  grad_tile_w();
 int  grad_tile_h();
 // k2_nms.cu
 void launch_frame_init(const Seeds & S, FrameCtrl * ctrl, int n_slots, cudaStream_t st);
 void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, const Planes & P, const Seeds & S,
-                FrameCtrl * ctrl, int n_slots, cudaStream_t st);
+                FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st);
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st);
 void nms_tile_dims(int * mw, int * mh, int * bw, int * bh);
 // k4_flood.cu

@@ -82,8 +82,15 @@ def run_case(eng, orc, name):
     l_ok = labels_equal_up_to_relabelling(labels, st["labels"])
     print(f"  labels         {'OK ' if l_ok else 'BAD'} px gpu {int((labels >= 0).sum())} ref {int((st['labels'] >= 0).sum())} exact={np.array_equal(labels, st['labels'])}")
     ok &= l_ok
-    ok &= cmp("comp_sizes", eng.fetch("comp_sizes"), st["comp_sizes"])
-    ok &= cmp("raw_segs", eng.fetch("raw_segs"), st["segs"])
+    cs, rs = eng.fetch("comp_sizes"), eng.fetch("raw_segs")
+    if not np.array_equal(seeds, st["seeds"]) and len(rs) == len(st["segs"]):
+        # seeds of exactly equal magnitude may be processed in either order (std::sort is unstable): compare as multisets
+        ka = np.lexsort((rs["y1"], rs["x1"])); kb = np.lexsort((st["segs"]["y1"], st["segs"]["x1"]))
+        ok &= cmp("comp_sizes(set)", cs[ka], st["comp_sizes"][kb])
+        ok &= cmp("raw_segs(set)", rs[ka], st["segs"][kb])
+    else:
+        ok &= cmp("comp_sizes", cs, st["comp_sizes"])
+        ok &= cmp("raw_segs", rs, st["segs"])
     ref = orc.find_line_segment_groups(img, min_length, seed=0)
     if ref is None:
         print("  oracle returns None; gpu n_lines", info["n_lines"])
