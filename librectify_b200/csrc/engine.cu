@@ -268,6 +268,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
 
     // ---- ingest (reference src/image.cpp:11-20: dense copy of a strided, possibly bottom-up buffer) ------------------
     stage(LRB_T_INGEST);
+    launch_frame_init(e->S, e->ctrl, n, e->st);
     CUtensorMap tm_user; const CUtensorMap * tm = &e->tm_img;
     Planes P1 = e->P; int tma_x = kMarginX, tma_y = kMarginY;      // K1's view: where the input image lives
     if (on_device) {
@@ -293,7 +294,6 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     }
     // ---- detection ---------------------------------------------------------------------------------------------------
     stage(LRB_T_GRAD);
-    launch_frame_init(e->S, e->ctrl, n, e->st);
     launch_grad(*tm, P1, e->ctrl, n, tma_x, tma_y, e->st);
     stage(LRB_T_NMS);
     launch_nms(e->tm_mag, e->tm_bin, e->P, e->S, e->ctrl, n, kMarginX, kMarginY, e->st);

@@ -1,0 +1,267 @@
+"""Parity of the CUDA hot path (through the C ABI) with the CPU oracle and the golden fixtures.  Needs a B200.
+
+Bars (BASELINE.json north_star): gradients, magnitudes, bins, dilated masks, NMS seeds, component labels,
+raw segments, the filtered set, the pencil model, sample pairs, per-hypothesis scores, winners, refits and group
+membership are all compared BIT-EXACT against the oracle; nothing here uses a floating-point tolerance except the
+explicitly marked corner test (<= 0.5 px, the north star's figure), which in practice also holds exactly.
+Seed order is compared modulo exact-magnitude ties (the reference's std::sort is unstable there).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests.util import labels_equal_up_to_relabelling, seeds_equal_modulo_ties
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def api():
+    from librectify_b200 import api as a
+    a.load_library()
+    return a
+
+
+@pytest.fixture(scope="module")
+def eng(api):
+    e = api.Engine(0, 1)
+    yield e
+    e.close()
+
+
+def _image_of(case):
+    return case["image"] if "image" in case else case["gray_u8"].astype(np.float32) / np.float32(256.0)
+
+
+def _synth(seed, w, h, **kw):
+    from librectify_b200.synth import manhattan_frame
+    return manhattan_frame(seed, w, h, **kw).numpy()
+
+
+def _ransac_trace(oracle, segs, T=10000):
+    n = len(segs)
+    samples = np.zeros((4, T, 2), np.int32); scores = np.zeros((4, T), np.float32); n_obs = np.zeros(4, np.int32)
+    winner = np.zeros(4, np.int32); best_h = np.zeros((4, 3), np.float32); refined = np.zeros((4, 3), np.float32)
+    groups = np.zeros(n, np.int32)
+    oracle.set_seed(0)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    k = oracle.lib.orc_ransac_trace(C.c_void_p(segs.ctypes.data), n, T, p(samples), p(scores), p(n_obs), p(winner), p(best_h), p(refined), p(groups))
+    return dict(k=k, samples=samples, scores=scores, n_obs=n_obs, winner=winner, best_h=best_h, refined=refined, groups=groups)
+
+
+def check_frame(api, eng, oracle, img, min_length):
+    """every stage of one frame against the oracle; returns the GPU segments"""
+    h, w = img.shape
+    info, lines = eng.detect(img, min_length)
+    info, lines = info[0], lines[0]
+    st = oracle.detect_stages(img, want_grad8=True)
+    for k in ("dx", "dy", "mag"):
+        assert np.array_equal(eng.fetch(k), st[k]), k                       # value-exact (+0 == -0)
+    assert np.array_equal(eng.fetch("bin").astype(np.int32), st["bin"])
+    # dilated masks: G_b(p) = mask8 bit b ? |dx sin + dy cos| : 0 must reproduce the reference's 8 masked energy planes
+    m8 = eng.fetch("mask8")
+    from tests.util import SIN8 as sn, COS8 as cs
+    for b in range(8):
+        g = np.abs(st["dx"] * sn[b] + st["dy"] * cs[b]).astype(np.float32)
+        g = np.where((m8 >> b) & 1, g, np.float32(0))
+        assert np.array_equal(g, st["grad8"][b]), f"masked energy plane {b}"
+    seeds = eng.fetch("seeds")
+    assert info["n_seeds"] == len(st["seeds"])
+    assert seeds_equal_modulo_ties(seeds, st["seeds"], st["mag"])
+    assert labels_equal_up_to_relabelling(eng.fetch("labels"), st["labels"])
+    cs_, rs = eng.fetch("comp_sizes"), eng.fetch("raw_segs")
+    assert len(rs) == len(st["segs"]) == info["n_components"]
+    if np.array_equal(seeds, st["seeds"]):
+        assert np.array_equal(cs_, st["comp_sizes"])
+        assert rs.tobytes() == st["segs"].tobytes()
+    else:   # exact-magnitude ties were ordered differently: same multiset of components
+        ka = np.lexsort((rs["y1"], rs["x1"])); kb = np.lexsort((st["segs"]["y1"], st["segs"]["x1"]))
+        assert np.array_equal(cs_[ka], st["comp_sizes"][kb]) and rs[ka].tobytes() == st["segs"][kb].tobytes()
+    ref = oracle.find_line_segment_groups(img, min_length, seed=0)
+    if ref is None:
+        assert info["n_lines"] == 0
+        return None
+    assert info["n_lines"] == len(ref) == len(lines)
+    geo = [f for f in api.SEG_DTYPE.names if f != "group_id"]
+    if not np.array_equal(seeds, st["seeds"]) and lines[geo].tobytes() != ref[geo].tobytes():
+        pytest.skip("exact-magnitude seed tie changed the segment order; grouping is not comparable")
+    assert lines[geo].tobytes() == ref[geo].tobytes()
+    m = oracle.pencil_model(ref)
+    assert np.array_equal(eng.fetch("model_h"), m["h"])
+    assert np.array_equal(eng.fetch("model_anchor"), m["anchor"])
+    assert np.array_equal(eng.fetch("model_dir"), m["dir"])
+    assert np.array_equal(eng.fetch("model_len"), m["len"])
+    assert np.array_equal(eng.fetch("model_bbox"), np.concatenate([m["bb"], m["center"], [m["scale"]]]).astype(np.float32))
+    tr = _ransac_trace(oracle, ref)
+    k = tr["k"]
+    g = eng.ransac_trace()
+    assert info["n_solves"] == k
+    assert np.array_equal(info["n_obs"][:k], tr["n_obs"][:k])
+    assert np.array_equal(g["winner"][:k], tr["winner"][:k])                # identical winners (first maximum in draw order)
+    assert np.array_equal(g["best_h"][:k], tr["best_h"][:k])
+    assert np.array_equal(g["refined"][:k], tr["refined"][:k])
+    assert np.array_equal(eng.fetch("scores")[:k], tr["scores"][:k])        # all 4 x 10^4 hypothesis scores
+    assert np.array_equal(eng.fetch("pairs"), tr["samples"][k - 1])         # identical sample sets
+    assert np.array_equal(lines["group_id"], ref["group_id"])               # identical membership
+    assert lines.tobytes() == ref.tobytes()
+    return lines
+
+
+@pytest.mark.parametrize("name", ["synth_320x240", "synth_640x360", "doc_image"])
+def test_golden_frames(api, eng, oracle, golden, name):
+    """committed fixtures produced by the compiled reference: stages vs oracle, final result vs the fixture bytes"""
+    case = golden(name)
+    img = _image_of(case)
+    lines = check_frame(api, eng, oracle, img, float(case["min_length"]))
+    assert lines.tobytes() == case["segs"].tobytes()
+    assert np.array_equal(eng.fetch("seeds"), case["seeds"])
+    assert eng.fetch("raw_segs").tobytes() == case["raw_segs"].tobytes()
+    h, w = img.shape
+    hmin = 2.0 if name == "doc_image" else 1.5
+    for hs in range(4):
+        for vs in range(4):
+            cfg = api.make_config(40.0, 1.5, vs, hmin, hs)
+            tf, _ = eng.rectify(img, float(case["min_length"]), cfg)
+            assert np.array_equal(api.tform_vec(tf[0]), case["tforms"][hs * 4 + vs], equal_nan=True), (hs, vs)
+
+
+@pytest.mark.parametrize("seed,w,h,nl", [(21, 333, 201, 20), (22, 517, 389, 30), (23, 1280, 720, 40), (1, 1920, 1080, 40)])
+def test_synthetic_frames(api, eng, oracle, seed, w, h, nl):
+    """odd widths (not multiples of 4 / 16 / the tile size) up to the 1080p configuration"""
+    check_frame(api, eng, oracle, _synth(seed, w, h, n_lines=nl), max(w, h) / 100.0)
+
+
+def test_corners_within_half_pixel_1080p(api, eng, oracle):
+    """north star: output corners within 0.5 px of the reference's at 1080p (tolerance stated here; observed: exact)"""
+    from oracle.bind import RectificationConfig, transform_to_dict
+    from tests.util import tform_vec
+    img = _synth(2, 1920, 1080)
+    tf, _ = eng.rectify(img, 19.2)
+    ref = oracle.find_line_segment_groups(img, 19.2, seed=0)
+    t = tform_vec(transform_to_dict(oracle.compute_rectification_transform(ref, 1920, 1080, RectificationConfig.default())))
+    a = api.tform_vec(tf[0])
+    assert np.max(np.abs(a[2:14] - t[2:14])) <= 0.5
+
+
+def test_sampler_known_answers(eng, oracle, golden):
+    """mt19937(0) + generate_canonical + Algorithm S"""
+    kat = golden("kat")
+    strm = eng.sample_pairs(10, 5)
+    assert strm[0].tolist() == [[8, 9], [5, 7], [7, 9], [0, 2], [1, 6]]
+    head = eng.fetch("stream", count=4)
+    assert (head / 2.0**32).astype(np.float32).tolist() == [np.float32(x) for x in (0.548813522, 0.592844605, 0.715189338, 0.844265759)]
+    for n, draws in ((940, 6258234), (1570, 10418421)):
+        p, d = eng.sample_pairs(n, 10000)
+        assert d == draws == int(kat[f"knuth_n{n}_draws"])
+        assert np.array_equal(p[:64], kat[f"knuth_n{n}_head"]) and np.array_equal(p[-1], kat[f"knuth_n{n}_tail"])
+        rp, rd, _ = oracle.choice_knuth(0, n, 10000)
+        assert np.array_equal(p, rp)
+    for n in (2, 3, 37, 20000):
+        p, d = eng.sample_pairs(n, 300)
+        rp, rd, _ = oracle.choice_knuth(0, n, 300)
+        assert np.array_equal(p, rp) and d == rd
+
+
+def test_other_seed(api, oracle):
+    """a different mt19937 seed: the stream is regenerated and the grouping follows the oracle's"""
+    img = _synth(31, 480, 270, n_lines=24)
+    try:
+        api.set_seed(77)
+        e = api.Engine(0, 1)
+        _, lines = e.detect(img, 5.0)
+        ref = oracle.find_line_segment_groups(img, 5.0, seed=77)
+        assert lines[0].tobytes() == ref.tobytes()
+        e.close()
+    finally:
+        api.set_seed(0)
+
+
+def test_drop_in_api_and_layouts(api, oracle, golden):
+    """reference librectify.h:15-18: (X, S) and (X + S*(H-1), -S) are equivalent; stride > width is honoured"""
+    case = golden("synth_320x240")
+    img = case["image"]
+    h, w = img.shape
+    out = api.find_line_segment_groups(img, 5.0)
+    assert out.tobytes() == case["segs"].tobytes()
+    pad = np.full((h, w + 7), 0.5, np.float32)
+    pad[:, :w] = img
+    for flipped in (False, True):
+        lib = api.load_library()
+        n = C.c_int(0)
+        stride = w + 7
+        base = pad.ctypes.data + (4 * stride * (h - 1) if flipped else 0)
+        ptr = lib.find_line_segment_groups(C.c_void_p(base), w, h, -stride if flipped else stride, C.c_float(5.0), False, 4, C.byref(n))
+        got = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_byte)), shape=(n.value * 28,)).view(api.SEG_DTYPE).copy()
+        p = C.c_void_p(ptr); lib.release_line_segments(C.byref(p))
+        assert not p.value and got.tobytes() == case["segs"].tobytes()
+
+
+def test_degenerate_inputs(api, eng):
+    """reference interface.cpp:50-54, 65-69: nullptr and *n_lines = 0"""
+    assert api.find_line_segment_groups(np.full((64, 96), 0.5, np.float32), 5.0) is None
+    tiny = np.zeros((5, 5), np.float32); tiny[2, 2] = 1
+    assert api.find_line_segment_groups(tiny, 5.0) is None
+    step = np.zeros((40, 40), np.float32); step[:, 20:] = 1.0
+    assert api.find_line_segment_groups(step, 100.0) is None
+    info, lines = eng.detect(step, 5.0)
+    assert info[0]["n_components"] >= 1
+
+
+def test_clean_edges_with_many_ties(api, eng, oracle):
+    """noise-free geometry: thousands of exactly equal magnitudes (tie groups) and long plateaus"""
+    img = np.full((200, 300), 0.25, np.float32)
+    img[40:160, 60:240] = 0.75
+    img[90:110, :] = 0.5
+    info, lines = eng.detect(img, 5.0)
+    st = oracle.detect_stages(img)
+    assert np.array_equal(eng.fetch("mag"), st["mag"]) and np.array_equal(eng.fetch("bin").astype(np.int32), st["bin"])
+    assert seeds_equal_modulo_ties(eng.fetch("seeds"), st["seeds"], st["mag"])
+    assert int((eng.fetch("labels") >= 0).sum()) > 0
+
+
+def test_batch_device_frames_match_single(api, oracle):
+    """device-resident batch (TMA straight from the caller's tensor, several slots per launch) == per-frame host calls;
+    a pitch that TMA cannot address (not a multiple of 16 bytes) goes through the ingest copy and gives the same result"""
+    import torch
+    from librectify_b200.synth import manhattan_frame
+    frames = torch.stack([manhattan_frame(40 + i, 640, 360, n_lines=30) for i in range(5)]).cuda()
+    e1 = api.Engine(0, 1); e4 = api.Engine(0, 4)
+    info4, lines4 = e4.detect(frames, 6.4)
+    for i in range(5):
+        _, l1 = e1.detect(frames[i].cpu().numpy(), 6.4)
+        assert l1[0].tobytes() == lines4[i].tobytes()
+        ref = oracle.find_line_segment_groups(frames[i].cpu().numpy(), 6.4, seed=0)
+        assert ref.tobytes() == lines4[i].tobytes()
+    odd = torch.zeros((5, 360, 643), device="cuda"); odd[:, :, :640] = frames
+    info_o, lines_o = e4.detect(odd[:, :, :640], 6.4)
+    for i in range(5):
+        assert lines_o[i].tobytes() == lines4[i].tobytes()
+    tf, _ = e4.rectify(frames, 6.4)
+    for i in range(5):
+        assert np.array_equal(api.tform_vec(tf[i]), api.tform_vec(api.compute_rectification_transform(lines4[i], 640, 360)), equal_nan=True)
+    e1.close(); e4.close()
+
+
+def test_idempotent_and_workspace_reuse(api, eng):
+    """the epoch-stamped ownership plane is reused across frames and sizes without clearing: results must not depend on history"""
+    a = _synth(50, 800, 450, n_lines=30); b = _synth(51, 640, 360, n_lines=30)
+    first = eng.detect(a, 8.0)[1][0].tobytes()
+    for _ in range(3):
+        eng.detect(b, 6.4)
+        assert eng.detect(a, 8.0)[1][0].tobytes() == first
+    for _ in range(40):          # enough frames to wrap the 8-bit epoch counter and force a plane re-initialisation
+        assert eng.detect(a, 8.0)[1][0].tobytes() == first
+
+
+def test_full_size_properties_4k(api, oracle):
+    """4K frame: too slow to trace hypothesis-by-hypothesis on the CPU in a unit test, so check the result itself
+    (segments + groups bit-exact vs the oracle's public entry point) and run-to-run determinism"""
+    img = _synth(3, 3840, 2160)
+    e = api.Engine(0, 1)
+    info, lines = e.detect(img, 38.4)
+    again = e.detect(img, 38.4)[1][0]
+    assert lines[0].tobytes() == again.tobytes()
+    ref = oracle.find_line_segment_groups(img, 38.4, seed=0)
+    assert lines[0].tobytes() == ref.tobytes()
+    e.close()

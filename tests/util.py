@@ -51,3 +51,10 @@ def labels_equal_up_to_relabelling(la, lb):
         return True
     pa = np.unique(np.stack([a, b], 1), axis=0)
     return len(pa) == len(np.unique(a)) == len(np.unique(b))
+
+
+# sin / cos of float(i*pi)/8 as float32 (pinned by the bit-exact grad8 digests in tests/golden)
+SIN8 = np.array([float.fromhex(x) for x in ("0x0p+0", "0x1.87de2cp-2", "0x1.6a09e6p-1", "0x1.d906bcp-1", "0x1p+0",
+                                            "0x1.d906bep-1", "0x1.6a09e6p-1", "0x1.87de2ep-2")], dtype=np.float32)
+COS8 = np.array([float.fromhex(x) for x in ("0x1p+0", "0x1.d906bcp-1", "0x1.6a09e6p-1", "0x1.87de2ap-2", "-0x1.777a5cp-25",
+                                            "-0x1.87de28p-2", "-0x1.6a09e6p-1", "-0x1.d906bcp-1")], dtype=np.float32)
