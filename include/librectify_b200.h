@@ -123,7 +123,8 @@ LRB_API void lrb_profile_read(lrb_engine * e, double * ms, long long * groups, l
 
 /* One uniform-stream sample run, for the sampler known-answer tests: `count` 2-subsets of [0,n) from the start of
  * the stream; returns the number of draws consumed (or negative on error). pairs: host int32 [count*2]. */
-LRB_API long long lrb_sample_pairs(lrb_engine * e, int n, int count, int * pairs);
+LRB_API long long lrb_sample_pairs(lrb_engine * e, int n, int count, int * pairs);            /* plain sequential walk */
+LRB_API long long lrb_sample_pairs_parallel(lrb_engine * e, int n, int count, int * pairs);   /* speculative workers + stitch */
 
 #ifdef __cplusplus
 }

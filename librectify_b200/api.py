@@ -74,6 +74,7 @@ def load_library(path: str | None = None):
     lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None
     lib.lrb_profile_read.argtypes = [vp, vp, vp, vp]; lib.lrb_profile_read.restype = None
     lib.lrb_sample_pairs.argtypes = [vp, ip, ip, vp]; lib.lrb_sample_pairs.restype = ll
+    lib.lrb_sample_pairs_parallel.argtypes = [vp, ip, ip, vp]; lib.lrb_sample_pairs_parallel.restype = ll
     # the drop-in symbols (reference names)
     lib.find_line_segment_groups.restype = vp
     lib.find_line_segment_groups.argtypes = [vp, ip, ip, ip, fp, C.c_bool, ip, C.POINTER(ip)]
@@ -271,9 +272,10 @@ class Engine:
         return dict(winner=raw[:4].copy(), best_h=raw[4:16].view(np.float32).reshape(4, 3).copy(),
                     refined=raw[16:28].view(np.float32).reshape(4, 3).copy())
 
-    def sample_pairs(self, n: int, count: int):
+    def sample_pairs(self, n: int, count: int, parallel: bool = False):
         pairs = np.zeros((count, 2), np.int32)
-        draws = self.lib.lrb_sample_pairs(self.h, n, count, pairs.ctypes.data)
+        fn = self.lib.lrb_sample_pairs_parallel if parallel else self.lib.lrb_sample_pairs
+        draws = fn(self.h, n, count, pairs.ctypes.data)
         if draws < 0:
             raise LibrectifyError(_err(self.lib))
         return pairs, int(draws)

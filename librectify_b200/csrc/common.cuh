@@ -48,6 +48,7 @@ __device__ __forceinline__ float orient_energy(float dx, float dy, int b)
 
 // ---- seed ordering ------------------------------------------------------------------------------------------------
 constexpr int kSeedBuckets = 4096;
+constexpr int kSampWorkers = 128, kSampRecords = 512;
 
 // ---- per-frame control block (device memory, one per slot; zeroed by k_frame_init) -------------------------------
 constexpr int kMaxRounds = 96;
@@ -75,6 +76,7 @@ struct FrameCtrl {
     float refined[kMaxModels][3];
     unsigned long long stream_pos;         // position in the shared uniform stream (carried across solves)
     int stream_overflow;
+    int samp_done;                         // samples already emitted by the parallel sampler (the sequential walk finishes the rest)
     float bbox[4], cx, cy, scale;
     int pad_[8];
 };
@@ -127,6 +129,12 @@ struct Lines {                  // per slot: filtered segments and the pencil mo
     int * tmp;                  // inlier list of the winning hypothesis
     int * pairs;                // 2 x T per slot: sampled positions in the observation list
     float * scores;             // kMaxModels x T per slot (-1 = rejected by sample_check); kept for the parity tests
+    // speculative sampler workers (k7_sampler.cu): kSampWorkers x kSampRecords records per slot
+    unsigned * rec_start;       // sample start, relative to the solve's first stream position
+    int * rec_pair;             // 2 per record: the two picks
+    int * rec_cnt1; int * rec_cnt;   // records made inside the own segment / in total
+    unsigned * rec_next;        // start of the sample after the last record
+    int * rec_link;             // 2 per worker: (worker, record) where the chain continues, worker < 0: none
 };
 
 constexpr int kMarginX = 0, kMarginY = 0;    // no margin needed: TMA accepts negative box origins (they only have to be 16-byte aligned in x)

@@ -24,9 +24,6 @@
 #include "common.cuh"
 #include "kernels.h"
 
-namespace lrb {
-void launch_sampler_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st);
-}
 
 using namespace lrb;
 
@@ -100,6 +97,7 @@ struct lrb_engine {
     int * labels = nullptr;            // debug plane (lazily used)
     CUtensorMap tm_img{}, tm_mag{}, tm_bin{};
     unsigned next_epoch = 0xFE;
+    int seed_div = 8;                  // seed capacity = pixels / seed_div; grown to 1 the first time a frame needs it
     // uniform stream
     unsigned * stream = nullptr; unsigned long long stream_len = 0; unsigned seed = 0;
     // bookkeeping of the last group
@@ -132,7 +130,7 @@ int ensure_stream(lrb_engine * e, unsigned long long need)
 // (re)allocate the workspace for frames of w x h
 int ensure_workspace(lrb_engine * e, int w, int h)
 {
-    if (e->arena && e->w == w && e->h == h) return 0;
+    if (e->arena && e->w == w && e->h == h && e->S.cap >= (int)std::min<size_t>((size_t)w * h / e->seed_div + 1024, (1u << 24) - 1)) return 0;
     if (w < 5 || h < 5 || w > 65535 || h > 65535) return fail(-1, "unsupported frame size %dx%d", w, h);
     if (e->arena) { CK(cudaStreamSynchronize(e->st)); CK(cudaFree(e->arena)); e->arena = nullptr; }
     const int G = e->slots;
@@ -140,7 +138,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     const size_t plane = (size_t)pitch * (h + kMarginY);
     const size_t org = (size_t)kMarginY * pitch + kMarginX;
     const size_t npx = (size_t)w * h;
-    const int cap_seeds = (int)std::min<size_t>(npx / 8 + 1024, (1u << 24) - 1);
+    const int cap_seeds = (int)std::min<size_t>(npx / e->seed_div + 1024, (1u << 24) - 1);
     const int cap_comp = (int)(npx / 6 + 16);
     const size_t cap_px = npx;
     const int cap_lines = cap_comp;
@@ -167,6 +165,10 @@ int ensure_workspace(lrb_engine * e, int w, int h)
         e->L.inlier = carve<int>(p, (size_t)cap_lines * G); e->L.garbage = carve<int>(p, (size_t)cap_lines * G);
         e->L.obs = carve<int>(p, (size_t)cap_lines * G); e->L.tmp = carve<int>(p, (size_t)cap_lines * G);
         e->L.pairs = carve<int>(p, (size_t)2 * kT * G); e->L.scores = carve<float>(p, (size_t)kMaxModels * kT * G);
+        const size_t nw = (size_t)kSampWorkers * G, nr = nw * kSampRecords;
+        e->L.rec_start = carve<unsigned>(p, nr); e->L.rec_pair = carve<int>(p, 2 * nr);
+        e->L.rec_cnt1 = carve<int>(p, nw); e->L.rec_cnt = carve<int>(p, nw); e->L.rec_next = carve<unsigned>(p, nw);
+        e->L.rec_link = carve<int>(p, 2 * nw);
         e->labels = carve<int>(p, npx);
         e->ctrl = carve<FrameCtrl>(p, G);
         return (size_t)(p - base);
@@ -213,7 +215,7 @@ void enqueue_tail(lrb_engine * e, int n, float min_length, int rounds_total, Tic
     launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds_total, e->st);
     tk.at(LRB_T_RANSAC);
     launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st);
-    e->kernels += 2 + 1 + 3 * kMaxModels + 1;
+    e->kernels += 2 + 1 + 6 * kMaxModels + 1;
 }
 
 int readback(lrb_engine * e, int n, Tick & tk)
@@ -238,6 +240,9 @@ void collect_profile(lrb_engine * e, const std::vector<int> & order)
         if (cudaEventElapsedTime(&ms, a, b) == cudaSuccess) e->ms[order[i]] += ms;
     }
 }
+
+int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w, int h, long long pitch,
+              long long fstride, float min_length);
 
 int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w, int h, long long pitch,
               long long fstride, float min_length)
@@ -326,7 +331,15 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         bool more_rounds = false, serial = false, more_stream = false;
         for (int i = 0; i < n; ++i) {
             const FrameCtrl & C = e->h_ctrl[i];
-            if (C.seed_overflow) { e->prof = prof_saved; return fail(-4, "frame %d: more than %d gradient peaks (seed capacity)", i, e->S.cap); }
+            if (C.seed_overflow == 2) { e->prof = prof_saved; return fail(-4, "frame %d: more than %d gradient peaks of (nearly) equal magnitude", i, 16384); }
+            if (C.seed_overflow) {
+                e->prof = prof_saved;
+                if (e->seed_div > 1) {                    // plateau-like input: every pixel can be a peak; enlarge the seed arrays once
+                    e->seed_div = 1;
+                    return run_group(e, frames, on_device, n, w, h, pitch, fstride, min_length);
+                }
+                return fail(-4, "frame %d: more than %d gradient peaks (seed capacity)", i, e->S.cap);
+            }
             if (C.comp_overflow || C.line_overflow) { e->prof = prof_saved; return fail(-4, "frame %d: component/segment capacity exceeded", i); }
             if (C.flood_overflow) serial = true;
             else if (!C.flood_done && C.live[rounds] != 0) more_rounds = true;

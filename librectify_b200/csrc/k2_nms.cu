@@ -212,6 +212,9 @@ __global__ void __launch_bounds__(256) k_seed_rank(Planes P, Seeds S, FrameCtrl 
     const unsigned m = S.b_mag[so + i], ix = S.b_idx[so + i];
     const int d = seed_bucket(__uint_as_float(m), thr, gmax);
     const int lo = S.start[bo + d], hi = lo + S.hist[bo + d];
+    // the in-bucket rank costs O(bucket^2); an input with tens of thousands of (nearly) equal magnitudes is rejected
+    // loudly instead of occupying the GPU for seconds
+    if (hi - lo > 16384) { ctrl[slot].seed_overflow = 2; return; }
     int before = 0;
     for (int j = lo; j < hi; ++j) {
         const unsigned mj = S.b_mag[so + j], ij = S.b_idx[so + j];

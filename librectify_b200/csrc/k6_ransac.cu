@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCt
         s_base = 0;
         // (re)start the grouping state: this kernel is also the entry point of a repair pass
         for (int k = 0; k < kMaxModels; ++k) { C.best[k] = 0ull; C.winner[k] = -1; C.n_obs[k] = 0; }
-        C.stream_pos = 0ull; C.stream_overflow = 0; C.n_solves = 0;
+        C.stream_pos = 0ull; C.stream_overflow = 0; C.n_solves = 0; C.samp_done = 0;
         if (floods_complete) C.fit_done = 1;             // the fit kernels ran on final floods: never redo them (they consume the owner stamps)
     }
     __syncthreads();
@@ -162,58 +162,6 @@ __global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCt
         L.dir[(lo + i) * 2 + 0] = __fdiv_rn(ddx, ln); L.dir[(lo + i) * 2 + 1] = __fdiv_rn(ddy, ln);
         L.inlier[lo + i] = -1; L.garbage[lo + i] = 0; L.obs[lo + i] = i;
     }
-}
-
-// ---- K7: Knuth Algorithm-S 2-subsets from the shared uniform stream ------------------------------------------------------
-// One warp per frame walks the stream once, 32 positions per step; the chain state (sample start o, picks so far m)
-// lives in registers, the stream is read strictly forward with the next chunks already in flight.
-constexpr int SMP_AHEAD = 8;
-
-__global__ void __launch_bounds__(32) k_sampler(Lines L, FrameCtrl * ctrl, const unsigned * __restrict__ stream,
-                                               unsigned long long stream_len, int solve, int T)
-{
-    const int slot = blockIdx.x;
-    FrameCtrl & C = ctrl[slot];
-    if (C.n_solves != solve || C.num_obs < 2) return;
-    const int lane = threadIdx.x;
-    const long long n = C.n_obs[solve];
-    int * pairs = L.pairs + (size_t)slot * 2 * T;
-    unsigned long long o = C.stream_pos;            // start of the current sample
-    unsigned long long cur = o;                     // first unconsumed stream position
-    unsigned long long base = o & ~31ull;
-    int m = 0, s0 = 0, done = 0;
-    unsigned kk[SMP_AHEAD];
-#pragma unroll
-    for (int a = 0; a < SMP_AHEAD; ++a) { const unsigned long long p = base + 32ull * a + lane; kk[a] = p < stream_len ? __ldg(stream + p) : 0u; }
-    bool overflow = false;
-    while (done < T) {
-#pragma unroll
-        for (int a = 0; a < SMP_AHEAD; ++a) {
-            if (done >= T) break;
-            const unsigned k = kk[a];
-            const unsigned long long p = base + lane;
-            if (base + 32 > stream_len) { overflow = true; done = T; break; }
-            // refill this register with the chunk SMP_AHEAD steps ahead before the dependent chain below
-            { const unsigned long long pn = p + 32ull * SMP_AHEAD; kk[a] = pn < stream_len ? __ldg(stream + pn) : 0u; }
-            while (true) {
-                const long long t = (long long)(p - o);                          // draws already made in this sample
-                const bool can = (p >= cur) && (t < n);
-                const bool sel = can && ((unsigned long long)(n - t) * (unsigned long long)k < ((unsigned long long)(2 - m) << 32));
-                const unsigned bm = __ballot_sync(0xffffffffu, sel);
-                if (bm == 0) break;
-                const int l = __ffs(bm) - 1;
-                const unsigned long long pos = base + l;
-                if (m == 0) { s0 = (int)(pos - o); m = 1; cur = pos + 1; }
-                else {
-                    if (lane == 0) { pairs[2 * done] = s0; pairs[2 * done + 1] = (int)(pos - o); }
-                    ++done; m = 0; o = pos + 1; cur = o;
-                    if (done >= T) break;
-                }
-            }
-            base += 32; if (cur < base) cur = base;
-        }
-    }
-    if (lane == 0) { C.stream_pos = o; if (overflow) C.stream_overflow = 1; }
 }
 
 // ---- K8: scoring grid -------------------------------------------------------------------------------------------------
@@ -392,16 +340,11 @@ void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int
     k_filter_model<<<n_slots, 1024, 0, st>>>(K, L, ctrl, min_length, rounds_total);
 }
 
-void launch_sampler_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st)
-{
-    k_sampler<<<1, 32, 0, st>>>(L, ctrl, stream, stream_len, 0, T);
-}
-
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
                    int T, cudaStream_t st)
 {
     for (int k = 0; k < kMaxModels; ++k) {
-        k_sampler<<<n_slots, 32, 0, st>>>(L, ctrl, stream, stream_len, k, T);
+        launch_sampler(L, ctrl, n_slots, stream, stream_len, k, T, st);
         dim3 gs((T + SC_THREADS - 1) / SC_THREADS, n_slots);
         k_score<<<gs, SC_THREADS, 0, st>>>(L, ctrl, k, T);
         k_refit_assign<<<n_slots, 1024, 0, st>>>(L, ctrl, k, T);

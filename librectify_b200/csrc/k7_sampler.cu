@@ -1,0 +1,256 @@
+// k7_sampler.cu — K7 `knuth_sampler`: the reference's sequential sampling chain, evaluated by 128 speculative workers.
+//
+// Replaces choice_knuth + the mt19937 draws inside RANSAC_Estimator::solve (reference src/math_utils.cpp:14-39,
+// src/estimator.h:46-50).  One RANSAC sample is a 2-subset of [0,n) by Knuth's Algorithm S:
+//     t = 0, m = 0;  while m < 2:  u = next uniform;  if (n - t) * u >= 2 - m: skip  else: pick t, ++m;   ++t
+// so a sample consumes a data-dependent number of draws (its second pick + 1), and the 10^4 samples of a solve form ONE
+// chain through the uniform stream: where sample i+1 starts depends on every draw before it.  The reference runs it
+// under an `omp critical`; a single warp needs milliseconds for it.
+//
+// Parallel restatement (exact):  "select at stream position p" for a sample that started at o depends only on
+// (p - o, m, k[p]), so ANY position can be tried as a sample start.  Worker j walks the chain speculatively from
+// s_j = o + j*L.  Two chains that ever start a sample at the same position are identical from there on, and chains
+// in the same neighbourhood coalesce within a handful of samples (a pick made because k[p] is very small is shared by
+// every chain that has not picked yet).  Phase 1: every worker records the samples that start inside its own segment
+// [s_j, s_j+1).  Phase 2: every worker keeps walking past the end of its segment until one of its sample starts is
+// found among the recorded starts of the segment it has reached — from there the next worker's record continues the
+// chain.  Phase 3: one warp follows the links from worker 0 (whose start IS the true chain start), which yields the
+// true samples in order, and writes the first T of them.  If some link is missing (tiny n, or no coalescence inside
+// the record capacity) the remaining samples are produced by the plain sequential walk — correct in every case.
+//
+// Integer-exact selection test: the stream stores k = 2^32 * u; select <=> (n-t) * k < (2-m) << 32.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace lrb {
+
+namespace {
+
+constexpr int SMP_AHEAD = 4;        // 32-position chunks kept in flight per warp
+
+// Walk the chain from sample start `o`, calling f(start, s0, s1, next_start) after every completed sample (warp-uniform
+// arguments); stops when f returns false.  Returns false if the stream ran out.
+template <class F>
+__device__ __forceinline__ bool chain_walk(const unsigned * __restrict__ stream, unsigned long long stream_len, long long n,
+                                           unsigned long long o, F f)
+{
+    const int lane = threadIdx.x & 31;
+    unsigned long long cur = o;                     // first unconsumed stream position
+    unsigned long long base = o & ~31ull;
+    int m = 0, s0 = 0;
+    unsigned kk[SMP_AHEAD];
+#pragma unroll
+    for (int a = 0; a < SMP_AHEAD; ++a) { const unsigned long long p = base + 32ull * a + lane; kk[a] = p < stream_len ? __ldg(stream + p) : 0u; }
+    while (true) {
+#pragma unroll
+        for (int a = 0; a < SMP_AHEAD; ++a) {
+            const unsigned k = kk[a];
+            const unsigned long long p = base + lane;
+            if (base + 32 > stream_len) return false;
+            { const unsigned long long pn = p + 32ull * SMP_AHEAD; kk[a] = pn < stream_len ? __ldg(stream + pn) : 0u; }
+            while (true) {
+                const long long t = (long long)(p - o);                          // draws already made in this sample
+                const bool can = (p >= cur) && (t < n);
+                const bool sel = can && ((unsigned long long)(n - t) * (unsigned long long)k < ((unsigned long long)(2 - m) << 32));
+                const unsigned bm = __ballot_sync(0xffffffffu, sel);
+                if (bm == 0) break;
+                const unsigned long long pos = base + (__ffs(bm) - 1);
+                if (m == 0) { s0 = (int)(pos - o); m = 1; cur = pos + 1; }
+                else {
+                    const unsigned long long start = o;
+                    const int s1 = (int)(pos - o);
+                    m = 0; o = pos + 1; cur = o;
+                    if (!f(start, s0, s1, o)) return true;
+                }
+            }
+            base += 32; if (cur < base) cur = base;
+        }
+    }
+}
+
+struct SamplerPlan { unsigned long long o0; unsigned long long L; long long n; };
+
+__device__ __forceinline__ SamplerPlan make_plan(const FrameCtrl & C, int solve, int T)
+{
+    SamplerPlan pl;
+    pl.n = C.n_obs[solve];
+    pl.o0 = C.stream_pos;
+    // expected draws of the whole solve: T * 2(n+1)/3 (the second pick of a 2-subset of [0,n) is at 2(n+1)/3 - 1 on
+    // average); relative spread over 10^4 samples ~0.4 %, so +3 % covers it — the last worker has no upper bound anyway
+    const unsigned long long D = (2ull * (unsigned long long)(pl.n + 1) * (unsigned long long)T) / 3ull;
+    pl.L = (D + D / 32) / kSampWorkers + 1;
+    return pl;
+}
+
+// ---- phase 1: samples that start inside the worker's own segment ----------------------------------------------------------
+__global__ void __launch_bounds__(32 * 4) k_sampler_segments(Lines L, FrameCtrl * ctrl, const unsigned * __restrict__ stream,
+                                                             unsigned long long stream_len, int solve, int T)
+{
+    const int slot = blockIdx.y;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    const int j = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (j >= kSampWorkers) return;
+    const int lane = threadIdx.x & 31;
+    const SamplerPlan pl = make_plan(C, solve, T);
+    const size_t ro = ((size_t)slot * kSampWorkers + j) * kSampRecords;
+    unsigned * rs = L.rec_start + ro; int2 * rp = reinterpret_cast<int2 *>(L.rec_pair) + ro;
+    const unsigned long long sj = pl.o0 + (unsigned long long)j * pl.L;
+    const unsigned long long send = (j == kSampWorkers - 1) ? ~0ull : sj + pl.L;
+    int cnt = 0;
+    unsigned long long next = sj;
+    const bool ok = chain_walk(stream, stream_len, pl.n, sj, [&](unsigned long long start, int s0, int s1, unsigned long long nx) {
+        if (lane == 0) { rs[cnt] = (unsigned)(start - pl.o0); rp[cnt] = make_int2(s0, s1); }
+        ++cnt; next = nx;
+        // the last worker runs until it alone could supply every sample that may still be missing, bounded by its record space
+        return (nx < send) && (cnt < kSampRecords - 1) && !(j == kSampWorkers - 1 && cnt >= T);
+    });
+    if (lane == 0) {
+        const size_t wo = (size_t)slot * kSampWorkers + j;
+        L.rec_cnt1[wo] = cnt; L.rec_cnt[wo] = cnt; L.rec_next[wo] = (unsigned)(next - pl.o0);
+        L.rec_link[2 * wo] = -1; L.rec_link[2 * wo + 1] = 0;
+        if (!ok && j == 0) C.stream_overflow = 1;      // only the true chain's own stretch must exist; speculative workers may fall off the end
+        if (!ok) L.rec_cnt1[wo] = -1 - cnt;            // mark "ran out of stream": nothing after its records is known
+    }
+}
+
+// ---- phase 2: walk on until a sample start is found among the starts recorded for the segment reached ----------------------
+__global__ void __launch_bounds__(32 * 4) k_sampler_link(Lines L, FrameCtrl * ctrl, const unsigned * __restrict__ stream,
+                                                         unsigned long long stream_len, int solve, int T)
+{
+    const int slot = blockIdx.y;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    const int j = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (j >= kSampWorkers - 1) return;                 // the last worker has no successor
+    const int lane = threadIdx.x & 31;
+    const SamplerPlan pl = make_plan(C, solve, T);
+    const size_t wo = (size_t)slot * kSampWorkers + j;
+    if (L.rec_cnt1[wo] < 0) return;                    // ran out of stream in phase 1
+    const size_t ro = wo * kSampRecords;
+    unsigned * rs = L.rec_start + ro; int2 * rp = reinterpret_cast<int2 *>(L.rec_pair) + ro;
+    int cnt = L.rec_cnt[wo];
+    if (cnt >= kSampRecords - 1) return;               // record space used up inside its own segment: no link
+
+    // is `start` (relative to o0) a recorded phase-1 sample start of the segment that contains it?
+    auto lookup = [&](unsigned rel, int & k_out) -> int {
+        int k = (int)min((unsigned long long)rel / pl.L, (unsigned long long)(kSampWorkers - 1));
+        k_out = k;
+        const size_t wk = (size_t)slot * kSampWorkers + k;
+        int c1 = L.rec_cnt1[wk]; if (c1 < 0) c1 = -1 - c1;
+        const unsigned * rk = L.rec_start + wk * kSampRecords;
+        int found = -1;
+        for (int i0 = 0; i0 < c1; i0 += 32) {
+            const int i = i0 + lane;
+            const unsigned bm = __ballot_sync(0xffffffffu, i < c1 && __ldg(rk + i) == rel);
+            if (bm) { found = i0 + __ffs(bm) - 1; break; }
+        }
+        return found;
+    };
+
+    unsigned long long next = pl.o0 + L.rec_next[wo];
+    int lk = -1, lb = 0;
+    { int k; const int b = lookup((unsigned)(next - pl.o0), k); if (b >= 0 && k != j) { lk = k; lb = b; } }
+    if (lk < 0) {
+        chain_walk(stream, stream_len, pl.n, next, [&](unsigned long long start, int s0, int s1, unsigned long long nx) {
+            if (lane == 0) { rs[cnt] = (unsigned)(start - pl.o0); rp[cnt] = make_int2(s0, s1); }
+            ++cnt; next = nx;
+            int k; const int b = lookup((unsigned)(nx - pl.o0), k);
+            if (b >= 0 && k != j) { lk = k; lb = b; return false; }
+            return cnt < kSampRecords - 1;
+        });
+    }
+    if (lane == 0) {
+        L.rec_cnt[wo] = cnt; L.rec_next[wo] = (unsigned)(next - pl.o0);
+        L.rec_link[2 * wo] = lk; L.rec_link[2 * wo + 1] = lb;
+    }
+}
+
+// ---- phase 3: follow the links from worker 0 and emit the first T samples in chain order -----------------------------------
+__global__ void __launch_bounds__(256) k_sampler_stitch(Lines L, FrameCtrl * ctrl, int solve, int T)
+{
+    __shared__ int s_w[kSampWorkers], s_b[kSampWorkers], s_c[kSampWorkers], s_off[kSampWorkers];
+    __shared__ int s_n, s_total;
+    const int slot = blockIdx.x;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    const size_t w0 = (size_t)slot * kSampWorkers;
+    if (threadIdx.x == 0) {
+        int cur = 0, b = 0, off = 0, nseg = 0;
+        unsigned long long endpos = C.stream_pos;
+        bool complete = false;
+        while (cur >= 0 && nseg < kSampWorkers) {
+            const int have = L.rec_cnt[w0 + cur] - b;                 // samples worker `cur` contributes from its entry point on
+            const int take = min(have, T - off);
+            s_w[nseg] = cur; s_b[nseg] = b; s_c[nseg] = take; s_off[nseg] = off; ++nseg;
+            off += take;
+            if (off >= T) {
+                // start of sample T = start of the record after the last one taken, or the worker's saved continuation
+                const int last = b + take;                             // index of the first record NOT taken
+                const unsigned rel = (last < L.rec_cnt[w0 + cur]) ? L.rec_start[(w0 + cur) * kSampRecords + last] : L.rec_next[w0 + cur];
+                endpos = C.stream_pos + rel; complete = true; break;
+            }
+            const int lk = L.rec_link[2 * (w0 + cur)];
+            if (lk < 0) { endpos = C.stream_pos + L.rec_next[w0 + cur]; break; }
+            b = L.rec_link[2 * (w0 + cur) + 1]; cur = lk;
+        }
+        s_n = nseg; s_total = off;
+        C.samp_done = off;                                           // < T: the sequential walk below finishes the job
+        C.stream_pos = endpos;
+        (void)complete;
+    }
+    __syncthreads();
+    int * pairs = L.pairs + (size_t)slot * 2 * T;
+    for (int s = 0; s < s_n; ++s) {
+        const int2 * rp = reinterpret_cast<const int2 *>(L.rec_pair) + (w0 + s_w[s]) * kSampRecords + s_b[s];
+        for (int i = threadIdx.x; i < s_c[s]; i += blockDim.x) {
+            const int2 v = rp[i];
+            pairs[2 * (s_off[s] + i)] = v.x; pairs[2 * (s_off[s] + i) + 1] = v.y;
+        }
+    }
+}
+
+// ---- sequential completion (and the whole job when called on its own): one warp per frame ----------------------------------
+__global__ void __launch_bounds__(32) k_sampler_tail(Lines L, FrameCtrl * ctrl, const unsigned * __restrict__ stream,
+                                                     unsigned long long stream_len, int solve, int T)
+{
+    const int slot = blockIdx.x;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    int done = C.samp_done;
+    if (done >= T) { if (threadIdx.x == 0) C.samp_done = 0; return; }
+    const int lane = threadIdx.x;
+    int * pairs = L.pairs + (size_t)slot * 2 * T;
+    unsigned long long next = C.stream_pos;
+    const bool ok = chain_walk(stream, stream_len, (long long)C.n_obs[solve], next, [&](unsigned long long, int s0, int s1, unsigned long long nx) {
+        if (lane == 0) { pairs[2 * done] = s0; pairs[2 * done + 1] = s1; }
+        ++done; next = nx;
+        return done < T;
+    });
+    if (lane == 0) { C.stream_pos = next; C.samp_done = 0; if (!ok) C.stream_overflow = 1; }
+}
+
+} // namespace
+
+void launch_sampler(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
+                    int solve, int T, cudaStream_t st)
+{
+    dim3 g((kSampWorkers + 3) / 4, n_slots);
+    k_sampler_segments<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
+    k_sampler_link<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
+    k_sampler_stitch<<<n_slots, 256, 0, st>>>(L, ctrl, solve, T);
+    k_sampler_tail<<<n_slots, 32, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
+}
+
+// known-answer entry: the plain sequential walk only (slot 0, solve 0)
+void launch_sampler_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st)
+{
+    k_sampler_tail<<<1, 32, 0, st>>>(L, ctrl, stream, stream_len, 0, T);
+}
+
+void launch_sampler_parallel_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st)
+{
+    launch_sampler(L, ctrl, 1, stream, stream_len, 0, T, st);
+}
+
+} // namespace lrb

@@ -28,6 +28,11 @@ void launch_labels(const Planes & P, const Comps & K, FrameCtrl * ctrl, int * la
 void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, cudaStream_t st);
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
                    int T, cudaStream_t st);
+// k7_sampler.cu
+void launch_sampler(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
+                    int solve, int T, cudaStream_t st);
+void launch_sampler_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st);
+void launch_sampler_parallel_only(const Lines & L, FrameCtrl * ctrl, const unsigned * stream, unsigned long long stream_len, int T, cudaStream_t st);
 // mt_stream.cu
 void launch_mt_stream(unsigned seed, unsigned * stream, unsigned long long n, cudaStream_t st);
 // ingest.cu

@@ -163,6 +163,17 @@ def test_sampler_known_answers(eng, oracle, golden):
         assert np.array_equal(p, rp) and d == rd
 
 
+@pytest.mark.parametrize("n", [2, 3, 4, 7, 14, 22, 58, 319, 940, 1570, 5000])
+def test_parallel_sampler_equals_sequential_chain(eng, oracle, n):
+    """the speculative-worker sampler (what the pipeline runs) reproduces the chain sample for sample, and leaves the
+    stream position (= mt19937 state carried to the next solve) where the sequential walk leaves it"""
+    for count in (10000, 777):
+        p, d = eng.sample_pairs(n, count, parallel=True)
+        rp, rd, _ = oracle.choice_knuth(0, n, count)
+        assert np.array_equal(p, rp), n
+        assert d == rd
+
+
 def test_other_seed(api, oracle):
     """a different mt19937 seed: the stream is regenerated and the grouping follows the oracle's"""
     img = _synth(31, 480, 270, n_lines=24)
