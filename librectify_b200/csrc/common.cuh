@@ -49,6 +49,7 @@ __device__ __forceinline__ float orient_energy(float dx, float dy, int b)
 // ---- seed ordering ------------------------------------------------------------------------------------------------
 constexpr int kSeedBuckets = 4096;
 constexpr int kSampWorkers = 128, kSampRecords = 512;
+constexpr int kFloodWindowMin = 4096, kFloodWindowDiv = 6;   // seeds flooded per round: max(4096, n_seeds / 6)
 
 // ---- per-frame control block (device memory, one per slot; zeroed by k_frame_init) -------------------------------
 constexpr int kMaxRounds = 96;
@@ -65,6 +66,8 @@ struct FrameCtrl {
     int rounds_run;
     int flood_done;            // set by the serial fallback
     int fit_done;              // components selected and fitted on final floods
+    int win_lo, win_hi;        // flood window: ranks processed by the current round
+    int win_live, win_first, win_blocks;   // commit-kernel scratch (live seeds left in the window, lowest of them, blocks done)
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
     // grouping state
     int num_obs;               // reference estimator.h:119

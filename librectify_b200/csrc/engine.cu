@@ -77,7 +77,7 @@ int make_tmap(CUtensorMap * m, CUtensorMapDataType dt, int esize, const void * b
 
 constexpr int kT = kRansacIter;
 constexpr int kLinesHead = 4096;       // segments per slot copied back together with the control block
-constexpr int kInitialRounds = 8;
+constexpr int kInitialRounds = 16;
 
 } // namespace
 

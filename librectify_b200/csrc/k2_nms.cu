@@ -179,7 +179,10 @@ __global__ void __launch_bounds__(1024) k_seed_scan(Seeds S, FrameCtrl * ctrl)
     *reinterpret_cast<int4 *>(cursor + 4 * t) = make_int4(0, 0, 0, 0);
     if (t == 0) {
         if (ctrl[slot].n_seeds > S.cap) { ctrl[slot].n_seeds = S.cap; ctrl[slot].seed_overflow = 1; }
-        ctrl[slot].live[0] = ctrl[slot].n_seeds;
+        const int ns = ctrl[slot].n_seeds;
+        ctrl[slot].live[0] = ns;
+        ctrl[slot].win_lo = 0; ctrl[slot].win_hi = min(ns, max(kFloodWindowMin, ns / kFloodWindowDiv));
+        ctrl[slot].win_live = 0; ctrl[slot].win_first = 0x7fffffff; ctrl[slot].win_blocks = 0;
     }
 }
 

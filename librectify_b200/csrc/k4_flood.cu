@@ -143,7 +143,10 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, Fra
     __syncwarp();
 }
 
-// persistent-style grid: warps stride over the seed ranks (low ranks = high priority first)
+// Rounds work on a WINDOW of the highest-priority live seeds (ranks [win_lo, win_hi)): every live seed outside the
+// window has lower priority than every seed inside, so it cannot influence what the window commits, and by the time its
+// turn comes most of it has been swallowed by a committed region (seeds along one line are dominated by the line's
+// strongest seed) and is dropped without ever flooding.  This keeps the work close to the sequential algorithm's.
 __global__ void __launch_bounds__(FL_WARPS * 32)
 k_flood_round(Planes P, Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_first)
 {
@@ -151,32 +154,51 @@ k_flood_round(Planes P, Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_fir
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
-    const int n = C.n_seeds;
+    const int lo = C.win_lo, hi = C.win_hi;
     const int warp = threadIdx.x >> 5;
     const unsigned epoch = epoch_first - (unsigned)round;
-    for (int rank = blockIdx.x * FL_WARPS + warp; rank < n; rank += gridDim.x * FL_WARPS)
+    for (int rank = lo + blockIdx.x * FL_WARPS + warp; rank < hi; rank += gridDim.x * FL_WARPS)
         flood_one(P, S, C, slot, rank, epoch, epoch_first, q[warp]);
 }
 
-// commit every live seed that nobody out-prioritised in this round; count what is still live
+// commit every window seed that nobody out-prioritised in this round; the last block to finish moves the window
 __global__ void __launch_bounds__(256)
 k_flood_commit(Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_first)
 {
+    __shared__ int s_last;
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
     const int n = C.n_seeds;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lo = C.win_lo, hi = C.win_hi;
     const unsigned epoch = epoch_first - (unsigned)round;
     const size_t so = (size_t)slot * S.cap;
-    int live = 0;
-    if (i < n && S.status[so + i] == kStatusLive) {
-        if (S.fail_epoch[so + i] != epoch) S.status[so + i] = (epoch << 24) | (unsigned)i;
-        else live = 1;
+    int live = 0, first = 0x7fffffff;
+    for (int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
+        if (S.status[so + i] == kStatusLive) {
+            if (S.fail_epoch[so + i] != epoch) S.status[so + i] = (epoch << 24) | (unsigned)i;
+            else { ++live; first = min(first, i); }
+        }
     }
-    const unsigned m = __ballot_sync(0xffffffffu, live);
-    if ((threadIdx.x & 31) == 0 && m) atomicAdd(&C.live[round + 1], __popc(m));
-    if (i == 0) C.rounds_run = round + 1;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { live += __shfl_xor_sync(0xffffffffu, live, s); first = min(first, __shfl_xor_sync(0xffffffffu, first, s)); }
+    if ((threadIdx.x & 31) == 0 && live) { atomicAdd(&C.win_live, live); atomicMin(&C.win_first, first); }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(&C.win_blocks, 1) == (int)gridDim.x - 1);
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        __threadfence();
+        const int failed = atomicAdd(&C.win_live, 0);                 // window seeds that stay live (out-prioritised this round)
+        const int firstf = atomicMin(&C.win_first, 0x7fffffff);
+        const int budget = max(kFloodWindowMin, n / kFloodWindowDiv);
+        const int nlo = failed ? min(firstf, hi) : hi;
+        const int nhi = min(n, hi + max(0, budget - failed));
+        C.win_lo = nlo; C.win_hi = nhi;
+        C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0;
+        C.live[round + 1] = failed + (n - hi);                       // seeds that may still have to flood
+        C.rounds_run = round + 1;
+    }
 }
 
 // Fallback when a speculative flood ran out of on-chip space or the epoch budget: the reference algorithm verbatim,
@@ -255,9 +277,9 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_firs
 void launch_flood_rounds(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint,
                          int round_begin, int round_end, unsigned epoch_first, cudaStream_t st)
 {
-    // flood: a few CTAs per SM striding over the ranks; commit: one thread per possible seed
+    // flood: CTAs striding over the window's ranks; commit: a fixed small grid striding over the window
     const int fblocks = max(1, min((seeds_hint + FL_WARPS - 1) / FL_WARPS, 148 * 4 / max(1, min(n_slots, 4))));
-    dim3 gf(fblocks, n_slots), gc((seeds_hint + 255) / 256, n_slots);
+    dim3 gf(fblocks, n_slots), gc(32, n_slots);
     for (int r = round_begin; r < round_end; ++r) {
         k_flood_round<<<gf, FL_WARPS * 32, 0, st>>>(P, S, ctrl, r, epoch_first);
         k_flood_commit<<<gc, 256, 0, st>>>(S, ctrl, r, epoch_first);

@@ -26,7 +26,7 @@ namespace lrb {
 
 namespace {
 
-constexpr int SMP_AHEAD = 4;        // 32-position chunks kept in flight per warp
+constexpr int SMP_AHEAD = 8;        // 32-position chunks kept in flight per warp
 
 // Walk the chain from sample start `o`, calling f(start, s0, s1, next_start) after every completed sample (warp-uniform
 // arguments); stops when f returns false.  Returns false if the stream ran out.
@@ -96,14 +96,13 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_segments(Lines L, FrameCtrl 
     const size_t ro = ((size_t)slot * kSampWorkers + j) * kSampRecords;
     unsigned * rs = L.rec_start + ro; int2 * rp = reinterpret_cast<int2 *>(L.rec_pair) + ro;
     const unsigned long long sj = pl.o0 + (unsigned long long)j * pl.L;
-    const unsigned long long send = (j == kSampWorkers - 1) ? ~0ull : sj + pl.L;
+    const unsigned long long send = sj + pl.L;      // the planned range already carries a 3 % (> 7 sigma) margin; beyond it the tail walk takes over
     int cnt = 0;
     unsigned long long next = sj;
     const bool ok = chain_walk(stream, stream_len, pl.n, sj, [&](unsigned long long start, int s0, int s1, unsigned long long nx) {
         if (lane == 0) { rs[cnt] = (unsigned)(start - pl.o0); rp[cnt] = make_int2(s0, s1); }
         ++cnt; next = nx;
-        // the last worker runs until it alone could supply every sample that may still be missing, bounded by its record space
-        return (nx < send) && (cnt < kSampRecords - 1) && !(j == kSampWorkers - 1 && cnt >= T);
+        return (nx < send) && (cnt < kSampRecords - 1);
     });
     if (lane == 0) {
         const size_t wo = (size_t)slot * kSampWorkers + j;
@@ -175,24 +174,30 @@ __global__ void __launch_bounds__(256) k_sampler_stitch(Lines L, FrameCtrl * ctr
     FrameCtrl & C = ctrl[slot];
     if (C.n_solves != solve || C.num_obs < 2) return;
     const size_t w0 = (size_t)slot * kSampWorkers;
+    __shared__ int t_cnt[kSampWorkers], t_lk[kSampWorkers], t_lb[kSampWorkers];
+    __shared__ unsigned t_next[kSampWorkers];
+    for (int i = threadIdx.x; i < kSampWorkers; i += blockDim.x) {
+        t_cnt[i] = L.rec_cnt[w0 + i]; t_lk[i] = L.rec_link[2 * (w0 + i)]; t_lb[i] = L.rec_link[2 * (w0 + i) + 1]; t_next[i] = L.rec_next[w0 + i];
+    }
+    __syncthreads();
     if (threadIdx.x == 0) {
         int cur = 0, b = 0, off = 0, nseg = 0;
         unsigned long long endpos = C.stream_pos;
         bool complete = false;
         while (cur >= 0 && nseg < kSampWorkers) {
-            const int have = L.rec_cnt[w0 + cur] - b;                 // samples worker `cur` contributes from its entry point on
+            const int have = t_cnt[cur] - b;                 // samples worker `cur` contributes from its entry point on
             const int take = min(have, T - off);
             s_w[nseg] = cur; s_b[nseg] = b; s_c[nseg] = take; s_off[nseg] = off; ++nseg;
             off += take;
             if (off >= T) {
                 // start of sample T = start of the record after the last one taken, or the worker's saved continuation
                 const int last = b + take;                             // index of the first record NOT taken
-                const unsigned rel = (last < L.rec_cnt[w0 + cur]) ? L.rec_start[(w0 + cur) * kSampRecords + last] : L.rec_next[w0 + cur];
+                const unsigned rel = (last < t_cnt[cur]) ? L.rec_start[(w0 + cur) * kSampRecords + last] : t_next[cur];
                 endpos = C.stream_pos + rel; complete = true; break;
             }
-            const int lk = L.rec_link[2 * (w0 + cur)];
-            if (lk < 0) { endpos = C.stream_pos + L.rec_next[w0 + cur]; break; }
-            b = L.rec_link[2 * (w0 + cur) + 1]; cur = lk;
+            const int lk = t_lk[cur];
+            if (lk < 0) { endpos = C.stream_pos + t_next[cur]; break; }
+            b = t_lb[cur]; cur = lk;
         }
         s_n = nseg; s_total = off;
         C.samp_done = off;                                           // < T: the sequential walk below finishes the job
