@@ -67,6 +67,7 @@ struct FrameCtrl {
     int flood_done;            // set by the serial fallback
     int fit_done;              // components selected and fitted on final floods
     int win_lo, win_hi;        // flood window: ranks processed by the current round
+    int pool_cursor;           // next free chunk of the pixel-list pool
     int win_live, win_first, win_blocks;   // commit-kernel scratch (live seeds left in the window, lowest of them, blocks done)
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
     // grouping state
@@ -94,6 +95,7 @@ struct Planes {                 // one frame slot = one set of planes; slot s li
     size_t img_stride; int img_pitch;
     float * dx; float * dy; float * mag;
     uint8_t * bin; uint8_t * mask8;
+    uint8_t * vis;              // visited mask of the flood (reference filter.cpp `visited`), cleared per frame
     unsigned * owner;
 };
 
@@ -107,6 +109,7 @@ struct Seeds {                  // per slot: s * cap
     unsigned * status;                        // 0 live, 1 dropped, else commit key
     unsigned * fail_epoch;
     int * size;
+    int * list_head;                          // first pool chunk of the seed's tentative pixel list (this round)
     int * hist; int * start; int * cursor;    // kSeedBuckets each per slot
 };
 
@@ -118,6 +121,7 @@ struct Comps {                  // per slot
     unsigned * px;              // pixel raster indices in the reference's BFS order
     float * val;                // G_bin at those pixels
     float * seg;                // raw LineSegment records (7 x 4 bytes each)
+    unsigned * pool; int cap_pool;   // per-round pixel lists of the tentative floods (32-word chunks)
 };
 
 struct Lines {                  // per slot: filtered segments and the pencil model built on them

@@ -141,24 +141,28 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     const int cap_seeds = (int)std::min<size_t>(npx / e->seed_div + 1024, (1u << 24) - 1);
     const int cap_comp = (int)(npx / 6 + 16);
     const size_t cap_px = npx;
+    const size_t cap_pool = (2 * npx + 65536) / 32 * 32;
     const int cap_lines = cap_comp;
     auto layout = [&](char * base) {
         char * p = base;
         e->ws_img_raw = carve<float>(p, plane * G); e->ws_img = e->ws_img_raw + org;
         e->P.dx = carve<float>(p, plane * G) + org; e->P.dy = carve<float>(p, plane * G) + org; e->P.mag = carve<float>(p, plane * G) + org;
         e->P.bin = carve<uint8_t>(p, plane * G) + org; e->P.mask8 = carve<uint8_t>(p, plane * G) + org;
+        e->P.vis = carve<uint8_t>(p, plane * G) + org;
         e->owner_raw = carve<unsigned>(p, plane * G); e->P.owner = e->owner_raw + org;
         e->S.us_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.us_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.b_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.b_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.idx = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.thr = carve<float>(p, (size_t)cap_seeds * G);
         e->S.bin = carve<uint8_t>(p, (size_t)cap_seeds * G); e->S.status = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.fail_epoch = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.size = carve<int>(p, (size_t)cap_seeds * G);
+        e->S.list_head = carve<int>(p, (size_t)cap_seeds * G);
         e->S.hist = carve<int>(p, (size_t)kSeedBuckets * G); e->S.start = carve<int>(p, (size_t)kSeedBuckets * G);
         e->S.cursor = carve<int>(p, (size_t)kSeedBuckets * G);
         e->K.rank = carve<int>(p, (size_t)cap_comp * G); e->K.off = carve<int>(p, (size_t)cap_comp * G);
         e->K.size = carve<int>(p, (size_t)cap_comp * G);
         e->K.px = carve<unsigned>(p, cap_px * G); e->K.val = carve<float>(p, cap_px * G);
         e->K.seg = carve<float>(p, (size_t)cap_comp * 7 * G);
+        e->K.pool = carve<unsigned>(p, cap_pool * G);
         e->L.seg = carve<float>(p, (size_t)cap_lines * 7 * G); e->L.h = carve<float>(p, (size_t)cap_lines * 3 * G);
         e->L.anchor = carve<float>(p, (size_t)cap_lines * 2 * G); e->L.dir = carve<float>(p, (size_t)cap_lines * 2 * G);
         e->L.len = carve<float>(p, (size_t)cap_lines * G);
@@ -180,7 +184,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     e->w = w; e->h = h; e->pitch = pitch; e->plane = plane;
     e->P.w = w; e->P.h = h; e->P.pitch = pitch; e->P.stride = plane; e->P.wq = (w + 3) / 4 * 4;
     e->P.img = e->ws_img; e->P.img_stride = plane; e->P.img_pitch = pitch;
-    e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->L.cap = cap_lines;
+    e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->K.cap_pool = (int)std::min<size_t>(cap_pool, 0x7fffffe0); e->L.cap = cap_lines;
     CK(cudaMemsetAsync(e->arena, 0, bytes, e->st));
     launch_fill_u32(e->owner_raw, plane * G, kOwnerInit, e->st);
     e->next_epoch = 0xFE;
@@ -274,6 +278,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     // ---- ingest (reference src/image.cpp:11-20: dense copy of a strided, possibly bottom-up buffer) ------------------
     stage(LRB_T_INGEST);
     launch_frame_init(e->S, e->ctrl, n, e->st);
+    CK(cudaMemsetAsync(e->P.vis - ((size_t)kMarginY * e->pitch + kMarginX), 0, e->plane * n, e->st));
     CUtensorMap tm_user; const CUtensorMap * tm = &e->tm_img;
     Planes P1 = e->P; int tma_x = kMarginX, tma_y = kMarginY;      // K1's view: where the input image lives
     if (on_device) {
@@ -306,7 +311,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     launch_seed_order(e->P, e->S, e->ctrl, n, e->S.cap, e->st);
     stage(LRB_T_FLOOD);
     int rounds = kInitialRounds;
-    launch_flood_rounds(e->P, e->S, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
+    launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
     e->kernels += 2 + 1 + 3 + 2 * rounds;
     if (debug_sync) {
         stage(LRB_T_FIT); launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds, e->st);
@@ -348,12 +353,12 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         if (!more_rounds && !serial && !more_stream) break;
         if (more_rounds && !serial) {
             if (rounds + 16 <= kMaxRounds) {
-                launch_flood_rounds(e->P, e->S, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
+                launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
                 e->kernels += 32; rounds += 16;
             } else serial = true;
         }
         if (serial) {
-            launch_flood_serial(e->P, e->S, e->K, e->ctrl, n, epoch_first, epoch_first - (unsigned)kMaxRounds - 1, e->st);
+            launch_flood_serial(e->P, e->S, e->K, e->ctrl, n, epoch_first - (unsigned)kMaxRounds - 1, e->st);
             e->kernels++;
             for (int i = 0; i < n; ++i) if (e->h_ctrl[i].flood_overflow || e->h_ctrl[i].live[rounds]) e->last_fallback[i] = 1;
         }

@@ -5,16 +5,22 @@
 // otherwise an 8-connected flood over G_b (b = the seed's bin; G_b(p) > 0.75f * G_b(seed)) claims every reached pixel
 // in a shared `visited` mask (1-px border pre-visited) — whether or not the component is kept (size > 5) afterwards.
 //
-// Parallel restatement (hard part 1): per round, every live seed floods TENTATIVELY against the visited
-// state of the previous rounds and stamps each reached pixel with atomicMin(owner, epoch:rank).  A seed commits iff no
-// higher-priority live seed stamped any of its pixels.  Since a tentative region can only shrink as more pixels become
-// visited, a conflict-free region is exactly the region the sequential algorithm would produce.  Each round the
-// highest-priority live seed commits, so the rounds terminate; in practice 6-8 rounds suffice.
+// Parallel restatement (hard part 1).  A round takes a WINDOW of the highest-priority live seeds.
+//   flood : every window seed floods TENTATIVELY against the visited mask of the previous rounds, stamps each reached
+//           pixel with a fire-and-forget atomicMin(owner, epoch:rank) and appends it to a pixel list.
+//   verify: a seed commits iff every pixel of its list still carries its own stamp, i.e. no higher-priority seed of
+//           the window reached any of them.  A tentative region can only shrink as more pixels become visited, so a
+//           conflict-free region IS the region the sequential algorithm produces.  Committed regions are written into
+//           the visited mask; the highest-priority window seed always commits, so rounds terminate.
+// Live seeds outside the window all have lower priority than every window seed, so they cannot change what the window
+// commits — and by the time their turn comes most of them lie inside a committed region (seeds along one line are
+// dominated by the line's strongest seed) and are dropped without ever flooding, as in the sequential algorithm.
 //
-// owner word = [epoch:8 | rank:24].  Epochs DEcrease from round to round (and frame to frame), so a newer stamp always
-// wins atomicMin over stale ones and the 4 B/px plane is re-initialised (0xFF..) only when the 8-bit epoch wraps.
-// "visited(p)" is never materialised: p is visited iff status[rank(owner[p])] == owner[p], i.e. the seed that stamped
-// it committed in exactly that epoch.  Conflicts are detected by whoever performs the second atomicMin on a pixel.
+// Latency is what bounds this stage (a 2000-px line is a 1000-level BFS), so the exploration loop touches only data
+// that is constant during a round — mask8, dx, dy and the visited mask — through the non-coherent L1 path; the owner
+// stamps are write-only here and are inspected by the verify kernel.  owner word = [epoch | rank]; epochs DEcrease from
+// round to round and frame to frame, so a newer stamp always wins over stale ones and the plane is re-initialised only
+// when the epoch field wraps.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -22,44 +28,47 @@ namespace lrb {
 
 namespace {
 
-constexpr int FL_WARPS = 8;
+constexpr int FL_WARPS = 4;
 constexpr int FL_QCAP  = 1024;    // BFS ring per warp: must hold three consecutive BFS levels (frontier-, not region-bound)
 
 // reference src/filter.cpp:113-116 neighbour order (dr, dc)
 static __device__ __constant__ const int kDr[8] = {0, 0, 1, -1, -1, -1, 1, 1};
 static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
 
-__device__ __forceinline__ bool is_visited(unsigned o, unsigned epoch_first, const unsigned * status)
+// Pixel lists live in a per-frame pool of 32-word chunks: word 0 = index of the next chunk + 1 (0: none), words 1..31 =
+// pixels as (row << 16 | col).  The pool is recycled every round.
+__device__ __forceinline__ int pool_alloc(FrameCtrl & C, int cap_chunks)
 {
-    if (owner_epoch(o) > epoch_first) return false;            // never stamped in this frame
-    return __ldcg(status + owner_rank(o)) == o;
+    int c = 0;
+    if ((threadIdx.x & 31) == 0) c = atomicAdd(&C.pool_cursor, 1);
+    c = __shfl_sync(0xffffffffu, c, 0);
+    return c < cap_chunks ? c : -1;
 }
 
-// one tentative flood of seed `rank` by one warp
-//
-// The warp runs a level-synchronous BFS over the seed's tentative region: each step expands up to four pixels of the
-// current level against their eight neighbours (32 candidates, one per lane).  The ring `q` keeps every pixel pushed
-// for the previous, the current and the next level.  A pixel this seed stamped is recognised by owner == key; a pixel
-// stamped by a higher-priority seed (it stays part of the tentative region and is explored through) cannot be, so it
-// is looked up in that three-level window instead — a neighbour of a level-L pixel always lies in level L-1, L or L+1.
-__device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, FrameCtrl & C, int slot, int rank,
-                                          unsigned epoch, unsigned epoch_first, unsigned * q)
+// one tentative flood of seed `rank` by one warp: level-synchronous BFS, up to four pixels of the current level are
+// expanded against their eight neighbours per step (one candidate per lane).  The ring keeps every pixel pushed for the
+// previous, the current and the next level; a neighbour of a level-L pixel lies in level L-1, L or L+1, so "already
+// reached" is a search in that window.
+__device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl & C, int slot, int rank,
+                                          unsigned epoch, unsigned * q)
 {
     const int lane = threadIdx.x & 31;
     const size_t so = (size_t)slot * S.cap;
-    unsigned * status = S.status + so;
-    if (__ldcg(status + rank) != kStatusLive) return;
+    if (__ldcg(S.status + so + rank) != kStatusLive) return;
 
     const size_t pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
-    const float * dx = P.dx + pbase; const float * dy = P.dy + pbase; const uint8_t * mask8 = P.mask8 + pbase;
+    const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
+    const uint8_t * mask8 = P.mask8 + pbase; const uint8_t * vis = P.vis + pbase;
+    unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
+    const int cap_chunks = K.cap_pool / 32;
 
     const unsigned key = (epoch << 24) | (unsigned)rank;
     const unsigned spx = S.idx[so + rank];
     const int sr = spx / P.w, sc = spx - sr * P.w;
     const size_t spo = (size_t)sr * P.pitch + sc;
-    if (is_visited(__ldcg(owner + spo), epoch_first, status)) {    // line_detector.cpp:103: seed already swallowed
-        if (lane == 0) status[rank] = kStatusDropped;
+    if (__ldg(vis + spo)) {                                   // line_detector.cpp:103: seed already swallowed
+        if (lane == 0) S.status[so + rank] = kStatusDropped;
         return;
     }
     const int b = S.bin[so + rank];
@@ -67,18 +76,12 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, Fra
     const float sb = kSin[b], cb = kCos[b];
 
     // the seed itself: G_b(seed) > 0.75 G_b(seed) holds by construction (filter.cpp:119-131)
-    bool failed = false, overflow = false;
-    if (lane == 0) {
-        const unsigned old = atomicMin(owner + spo, key);
-        if (owner_epoch(old) == epoch) {
-            if (old < key) failed = true;                                   // a higher-priority seed already reached this pixel
-            else if (old != key) S.fail_epoch[so + owner_rank(old)] = epoch;
-        }
-        q[0] = ((unsigned)sr << 16) | (unsigned)sc;
-    }
+    if (lane == 0) { atomicMin(owner + spo, key); q[0] = ((unsigned)sr << 16) | (unsigned)sc; }
     __syncwarp();
     int head = 0, tail = 1;                 // absolute positions in the push sequence; ring index = pos & (FL_QCAP-1)
     int s_prev = 0, s_cur = 0, s_next = 1;  // first push of the previous / current / next BFS level
+    int flushed = 0, first_chunk = -1, last_chunk = -1;
+    bool overflow = false;
 
     while (head < tail) {
         if (head >= s_next) { s_prev = s_cur; s_cur = s_next; s_next = tail; }
@@ -90,65 +93,59 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, Fra
         const int r = (int)(prc >> 16) + kDr[k], c = (int)(prc & 0xFFFFu) + kDc[k];
         bool elig = act && r >= 1 && r < P.h - 1 && c >= 1 && c < P.w - 1;      // filter.cpp:101-107: border is visited
         const size_t po = (size_t)(elig ? r : 0) * P.pitch + (elig ? c : 0);
-        if (elig) elig = (__ldg(mask8 + po) >> b) & 1;                          // dilated bin mask, else G_b = 0
         if (elig) {
-            const float g = fabsf(__fadd_rn(__fmul_rn(__ldg(dx + po), sb), __fmul_rn(__ldg(dy + po), cb)));
-            elig = g > thr;                                                     // filter.cpp:131
+            const unsigned m8 = __ldg(mask8 + po), v = __ldg(vis + po);
+            const float gx = __ldg(dx + po), gy = __ldg(dy + po);
+            const float g = fabsf(__fadd_rn(__fmul_rn(gx, sb), __fmul_rn(gy, cb)));
+            elig = ((m8 >> b) & 1u) && !v && (g > thr);                         // dilated bin mask, not visited, filter.cpp:131
         }
-        unsigned o = 0;
-        if (elig) {
-            o = __ldcg(owner + po);
-            if (o == key) elig = false;                                         // already in this region
-            else if (is_visited(o, epoch_first, status)) elig = false;
-        }
-        // the same pixel may be reached from several parents in one step: lowest lane handles it
         const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
-        const unsigned long long mkey = elig ? (unsigned long long)rcq : ((1ull << 40) | (unsigned)lane);
-        const unsigned same = __match_any_sync(0xffffffffu, mkey);
-        const bool leader = elig && (lane == __ffs(same) - 1);
-        bool reached = false, lostcand = false;
-        if (leader) {
-            if (owner_epoch(o) == epoch && o < key) lostcand = true;            // stamped this round by a higher-priority seed
-            else {
-                const unsigned old = atomicMin(owner + po, key);
-                if (old == key) { /* cannot happen after de-duplication */ }
-                else if (owner_epoch(old) == epoch) {
-                    if (old < key) lostcand = true;
-                    else { S.fail_epoch[so + owner_rank(old)] = epoch; reached = true; }   // the other seed loses
-                } else reached = true;
-            }
-        }
-        if (lostcand) {                                                         // not ours: was it pushed in the last three levels?
-            failed = true;
+        if (elig) {                                                             // reached before (previous / this / next level)?
             bool seen = false;
             for (int i = s_prev; i < tail; ++i) seen |= (q[i & (FL_QCAP - 1)] == rcq);
-            reached = !seen;                                                    // still part of the tentative region: explore through it
+            elig = !seen;
         }
+        // the same pixel may be reached from several parents in one step: lowest lane handles it
+        const unsigned long long mkey = elig ? (unsigned long long)rcq : ((1ull << 40) | (unsigned)lane);
+        const unsigned same = __match_any_sync(0xffffffffu, mkey);
+        const bool reached = elig && (lane == __ffs(same) - 1);
+        if (reached) atomicMin(owner + po, key);                                // result unused: a reduction, off the critical path
         const unsigned pm = __ballot_sync(0xffffffffu, reached);
         const int np = __popc(pm);
-        if (tail + np - s_prev > FL_QCAP) { overflow = true; break; }           // the ring must keep three levels
+        if (tail + np - min(s_prev, flushed) > FL_QCAP) { overflow = true; break; }   // the ring must keep three levels + unflushed pixels
         if (reached) q[(tail + __popc(pm & ((1u << lane) - 1))) & (FL_QCAP - 1)] = rcq;
         tail += np;
         __syncwarp();
-    }
-
-    failed = __any_sync(0xffffffffu, failed);
-    if (lane == 0) {
-        if (overflow) { C.flood_overflow = 1; S.fail_epoch[so + rank] = epoch; }
-        else {
-            if (failed) S.fail_epoch[so + rank] = epoch;
-            S.size[so + rank] = tail;
+        // spill completed groups of 31 pixels to the pool
+        while (tail - flushed >= 31) {
+            const int ch = pool_alloc(C, cap_chunks);
+            if (ch < 0) { overflow = true; break; }
+            pool[(size_t)ch * 32 + lane] = lane ? q[(flushed + lane - 1) & (FL_QCAP - 1)] : 0u;
+            if (lane == 0 && last_chunk >= 0) pool[(size_t)last_chunk * 32] = (unsigned)ch + 1u;
+            if (first_chunk < 0) first_chunk = ch;
+            last_chunk = ch; flushed += 31;
         }
+        if (overflow) break;
+    }
+    if (!overflow && tail > flushed) {                                          // the last, partial chunk
+        const int ch = pool_alloc(C, cap_chunks);
+        if (ch < 0) overflow = true;
+        else {
+            pool[(size_t)ch * 32 + lane] = (lane && flushed + lane - 1 < tail) ? q[(flushed + lane - 1) & (FL_QCAP - 1)] : 0u;
+            if (lane == 0 && last_chunk >= 0) pool[(size_t)last_chunk * 32] = (unsigned)ch + 1u;
+            if (first_chunk < 0) first_chunk = ch;
+        }
+    }
+    if (lane == 0) {
+        if (overflow) C.flood_overflow = 1;
+        S.size[so + rank] = overflow ? -1 : tail;
+        S.list_head[so + rank] = first_chunk;
     }
     __syncwarp();
 }
 
-// Rounds work on a WINDOW of the highest-priority live seeds (ranks [win_lo, win_hi)): every live seed outside the
-// window has lower priority than every seed inside, so it cannot influence what the window commits, and by the time its
-// turn comes most of it has been swallowed by a committed region (seeds along one line are dominated by the line's
-// strongest seed) and is dropped without ever flooding.  This keeps the work close to the sequential algorithm's.
 __global__ void __launch_bounds__(FL_WARPS * 32)
-k_flood_round(Planes P, Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_first)
+k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first)
 {
     __shared__ unsigned q[FL_WARPS][FL_QCAP];
     const int slot = blockIdx.y;
@@ -158,12 +155,12 @@ k_flood_round(Planes P, Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_fir
     const int warp = threadIdx.x >> 5;
     const unsigned epoch = epoch_first - (unsigned)round;
     for (int rank = lo + blockIdx.x * FL_WARPS + warp; rank < hi; rank += gridDim.x * FL_WARPS)
-        flood_one(P, S, C, slot, rank, epoch, epoch_first, q[warp]);
+        flood_one(P, S, K, C, slot, rank, epoch, q[warp]);
 }
 
-// commit every window seed that nobody out-prioritised in this round; the last block to finish moves the window
+// verify + commit + mark visited, one warp per window seed; the last block to finish moves the window
 __global__ void __launch_bounds__(256)
-k_flood_commit(Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_first)
+k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first)
 {
     __shared__ int s_last;
     const int slot = blockIdx.y;
@@ -172,17 +169,40 @@ k_flood_commit(Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_first)
     const int n = C.n_seeds;
     const int lo = C.win_lo, hi = C.win_hi;
     const unsigned epoch = epoch_first - (unsigned)round;
-    const size_t so = (size_t)slot * S.cap;
+    const size_t so = (size_t)slot * S.cap, pbase = (size_t)slot * P.stride;
+    const unsigned * owner = P.owner + pbase;
+    uint8_t * vis = P.vis + pbase;
+    const unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     int live = 0, first = 0x7fffffff;
-    for (int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
-        if (S.status[so + i] == kStatusLive) {
-            if (S.fail_epoch[so + i] != epoch) S.status[so + i] = (epoch << 24) | (unsigned)i;
-            else { ++live; first = min(first, i); }
+    for (int rank = lo + blockIdx.x * nw + warp; rank < hi; rank += gridDim.x * nw) {
+        if (S.status[so + rank] != kStatusLive) continue;
+        const unsigned key = (epoch << 24) | (unsigned)rank;
+        const int size = S.size[so + rank];
+        // pass 1: is every pixel still stamped with this seed's key?
+        bool mine = true;
+        int left = size;
+        for (int ch = S.list_head[so + rank]; ch >= 0 && left > 0; ) {
+            const unsigned w = __ldcg(pool + (size_t)ch * 32 + lane);
+            const int here = min(left, 31);
+            if (lane >= 1 && lane <= here) mine &= (__ldcg(owner + (size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)) == key);
+            left -= here;
+            ch = (int)__shfl_sync(0xffffffffu, w, 0) - 1;
         }
+        mine = __all_sync(0xffffffffu, mine);
+        if (!mine) { ++live; first = min(first, rank); continue; }
+        // pass 2: the region is final — it becomes part of the visited mask (whether or not it is kept later)
+        left = size;
+        for (int ch = S.list_head[so + rank]; ch >= 0 && left > 0; ) {
+            const unsigned w = __ldcg(pool + (size_t)ch * 32 + lane);
+            const int here = min(left, 31);
+            if (lane >= 1 && lane <= here) vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
+            left -= here;
+            ch = (int)__shfl_sync(0xffffffffu, w, 0) - 1;
+        }
+        if (lane == 0) S.status[so + rank] = key;
     }
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) { live += __shfl_xor_sync(0xffffffffu, live, s); first = min(first, __shfl_xor_sync(0xffffffffu, first, s)); }
-    if ((threadIdx.x & 31) == 0 && live) { atomicAdd(&C.win_live, live); atomicMin(&C.win_first, first); }
+    if (lane == 0 && live) { atomicAdd(&C.win_live, live); atomicMin(&C.win_first, first); }
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) s_last = (atomicAdd(&C.win_blocks, 1) == (int)gridDim.x - 1);
@@ -195,16 +215,16 @@ k_flood_commit(Seeds S, FrameCtrl * ctrl, int round, unsigned epoch_first)
         const int nlo = failed ? min(firstf, hi) : hi;
         const int nhi = min(n, hi + max(0, budget - failed));
         C.win_lo = nlo; C.win_hi = nhi;
-        C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0;
+        C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0; C.pool_cursor = 0;
         C.live[round + 1] = failed + (n - hi);                       // seeds that may still have to flood
         C.rounds_run = round + 1;
     }
 }
 
-// Fallback when a speculative flood ran out of on-chip space or the epoch budget: the reference algorithm verbatim,
-// one warp per frame, seeds strictly in order, queue in global memory (capacity = one entry per pixel).
+// Fallback when a speculative flood ran out of on-chip or pool space, or the round budget: the reference algorithm
+// verbatim, one warp per frame, seeds strictly in order, queue in global memory (capacity = one entry per pixel).
 __global__ void __launch_bounds__(32)
-k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_first, unsigned epoch_serial)
+k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_serial)
 {
     const int slot = blockIdx.x;
     FrameCtrl & C = ctrl[slot];
@@ -214,6 +234,7 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_firs
     unsigned * status = S.status + so;
     const size_t pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
+    uint8_t * vis = P.vis + pbase;
     const float * dx = P.dx + pbase; const float * dy = P.dy + pbase; const uint8_t * mask8 = P.mask8 + pbase;
     unsigned * q = K.px + (size_t)slot * K.cap_px;             // not in use yet at this stage
 
@@ -222,7 +243,7 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_firs
         const unsigned key = (epoch_serial << 24) | (unsigned)rank;
         const unsigned spx = S.idx[so + rank];
         const int sr = spx / P.w, sc = spx - sr * P.w;
-        if (is_visited(__ldcg(owner + (size_t)sr * P.pitch + sc), epoch_first, status)) {
+        if (__ldcg(vis + (size_t)sr * P.pitch + sc)) {
             if (lane == 0) status[rank] = kStatusDropped;
             __syncwarp();
             continue;
@@ -251,10 +272,7 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_firs
                 const float g = fabsf(__fadd_rn(__fmul_rn(__ldg(dx + po), sb), __fmul_rn(__ldg(dy + po), cb)));
                 elig = g > thr;
             }
-            if (elig) {
-                const unsigned o = __ldcg(owner + po);
-                if (o == key || is_visited(o, epoch_first, status)) elig = false;
-            }
+            if (elig) elig = (__ldcg(vis + po) == 0) && (__ldcg(owner + po) != key);
             const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
             const unsigned long long mkey = elig ? (unsigned long long)rcq : ((1ull << 40) | (unsigned)lane);
             const unsigned same = __match_any_sync(0xffffffffu, mkey);
@@ -266,6 +284,10 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_firs
             first = false;
             __syncwarp();
         }
+        for (int i = lane; i < tail; i += 32) {                 // the region is final: visited
+            const unsigned w = __ldcg(q + i);
+            __stcg(vis + (size_t)(w >> 16) * P.pitch + (w & 0xFFFFu), (uint8_t)1);
+        }
         if (lane == 0) { S.size[so + rank] = tail; __stcg(status + rank, key); }
         __syncwarp();
     }
@@ -274,22 +296,22 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_firs
 
 } // namespace
 
-void launch_flood_rounds(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint,
+void launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int seeds_hint,
                          int round_begin, int round_end, unsigned epoch_first, cudaStream_t st)
 {
-    // flood: CTAs striding over the window's ranks; commit: a fixed small grid striding over the window
-    const int fblocks = max(1, min((seeds_hint + FL_WARPS - 1) / FL_WARPS, 148 * 4 / max(1, min(n_slots, 4))));
-    dim3 gf(fblocks, n_slots), gc(32, n_slots);
+    // flood: CTAs striding over the window's ranks; verify: warps striding over the window
+    const int fblocks = max(1, min((seeds_hint + FL_WARPS - 1) / FL_WARPS, 148 * 8 / max(1, min(n_slots, 4))));
+    dim3 gf(fblocks, n_slots), gv(148 / max(1, min(n_slots, 4)) + 1, n_slots);
     for (int r = round_begin; r < round_end; ++r) {
-        k_flood_round<<<gf, FL_WARPS * 32, 0, st>>>(P, S, ctrl, r, epoch_first);
-        k_flood_commit<<<gc, 256, 0, st>>>(S, ctrl, r, epoch_first);
+        k_flood_round<<<gf, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first);
+        k_flood_verify<<<gv, 256, 0, st>>>(P, S, K, ctrl, r, epoch_first);
     }
 }
 
 void launch_flood_serial(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots,
-                         unsigned epoch_first, unsigned epoch_serial, cudaStream_t st)
+                         unsigned epoch_serial, cudaStream_t st)
 {
-    k_flood_serial<<<n_slots, 32, 0, st>>>(P, S, K, ctrl, epoch_first, epoch_serial);
+    k_flood_serial<<<n_slots, 32, 0, st>>>(P, S, K, ctrl, epoch_serial);
 }
 
 } // namespace lrb

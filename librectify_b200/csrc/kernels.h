@@ -17,10 +17,10 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st);
 void nms_tile_dims(int * mw, int * mh, int * bw, int * bh);
 // k4_flood.cu
-void launch_flood_rounds(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint,
+void launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int seeds_hint,
                          int round_begin, int round_end, unsigned epoch_first, cudaStream_t st);
 void launch_flood_serial(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots,
-                         unsigned epoch_first, unsigned epoch_serial, cudaStream_t st);
+                         unsigned epoch_serial, cudaStream_t st);
 // k5_fit.cu
 void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int rounds_total, cudaStream_t st);
 void launch_labels(const Planes & P, const Comps & K, FrameCtrl * ctrl, int * labels, int slot, cudaStream_t st);
