@@ -30,10 +30,10 @@ constexpr int K1_TW = 128;          // tile width  (32 lanes x 4 columns)
 constexpr int K1_HALO_L = 4;        // staged columns left of the tile: 2 needed, 4 keeps the TMA box origin 16-byte aligned
 constexpr int K1_SW = K1_HALO_L + K1_TW + 4;   // staged width (544 B rows: multiple of 16 B as TMA requires)
 
+template <bool INTERIOR>
 __device__ __forceinline__ void finish_pixel(float dx, float dy, bool valid, float & odx, float & ody, float & omag, unsigned & obin)
 {
-    dx = valid ? dx : 0.0f;
-    dy = valid ? dy : 0.0f;
+    if (!INTERIOR) { dx = valid ? dx : 0.0f; dy = valid ? dy : 0.0f; }        // conv_2d leaves the 2-px border at 0 (filter.cpp:81-98)
     odx = dx; ody = dy;
     omag = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));      // line_detector.cpp:47
     // eight orientation energies |dx*sin(t_i) + dy*cos(t_i)|, t_i = float(i*pi)/8 (line_detector.cpp:142-146).
@@ -51,14 +51,119 @@ __device__ __forceinline__ void finish_pixel(float dx, float dy, bool valid, flo
     g[6] = fabsf(__fsub_rn(dxs2, dys2));                                     // dy*(-s2) == -(dy*s2)
     g[7] = fabsf(__fsub_rn(__fmul_rn(dx, S7), dyc1));                        // dy*(-c1) == -(dy*c1)
     // first strict maximum with the running maximum initialised to 0 (line_detector.cpp:152-156)
-    float gm = 0.0f; unsigned b = 0;
+    float gm = g[0]; unsigned b = 0;                                         // g[0] > 0 selects bin 0, which is also the default
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { if (g[i] > gm) { b = i; gm = g[i]; } }
+    for (int i = 1; i < 8; ++i) { b = (g[i] > gm) ? (unsigned)i : b; gm = fmaxf(gm, g[i]); }
     obin = b;
 }
 
+// One tap row of both filters for one output pixel column c: `first` starts the sums (tap row 0).
+// Hx row a: -K[ar][0], -K[ar][1], 0, +K[ar][1], +K[ar][0];  Hy row a: sign(a-2) * {K[0][ac], K[1][ac], K[2][ac], K[1][ac], K[0][ac]}
+template <int A>
+__device__ __forceinline__ void tap_row(const float (&m)[3][2][8], float (&sx)[4], float (&sy)[4])
+{
+    constexpr int ar = A < 2 ? A : 4 - A;       // 0,1,2,1,0
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        float x = (A == 0) ? -m[ar][0][c] : __fsub_rn(sx[c], m[ar][0][c]);
+        x = __fsub_rn(x, m[ar][1][c + 1]);
+        x = __fadd_rn(x, m[ar][1][c + 3]);
+        x = __fadd_rn(x, m[ar][0][c + 4]);
+        sx[c] = x;
+        if (A != 2) {
+            constexpr int ac = ar;              // 0 or 1 here
+            float y;
+            if (A < 2) {
+                y = (A == 0) ? -m[0][ac][c] : __fsub_rn(sy[c], m[0][ac][c]);
+                y = __fsub_rn(y, m[1][ac][c + 1]);
+                y = __fsub_rn(y, m[2][ac][c + 2]);
+                y = __fsub_rn(y, m[1][ac][c + 3]);
+                y = __fsub_rn(y, m[0][ac][c + 4]);
+            } else {
+                y = __fadd_rn(sy[c], m[0][ac][c]);
+                y = __fadd_rn(y, m[1][ac][c + 1]);
+                y = __fadd_rn(y, m[2][ac][c + 2]);
+                y = __fadd_rn(y, m[1][ac][c + 3]);
+                y = __fadd_rn(y, m[0][ac][c + 4]);
+            }
+            sy[c] = y;
+        }
+    }
+}
+
+// The row loop is deliberately NOT unrolled: a fully unrolled 12-row body is ~70 KB of SASS, far beyond the 32 KB
+// instruction cache level (ncu: 24 % instruction-cache misses, issue slots 65-75 % busy).  Instead the five partially
+// accumulated output rows live in "role" registers — role a holds the output row whose next tap row is a — and shift by
+// one role per input row, so the loop body (~8 KB) stays cache resident.
+template <int RPT, bool INTERIOR>
+__device__ __forceinline__ float compute_strip(const float * tile, const Planes & P, int slot, int x0, int y0, int lane, int warp)
+{
+    const int ty0 = warp * RPT;                 // first output row of this thread inside the tile
+    const int xq = x0 + lane * 4;               // first output column
+    float rx[5][4], ry[5][4];                   // role registers
+    float tmax = 0.0f;
+    // column validity of the four output columns (2-px border), hoisted out of the row loop
+    const bool vc0 = INTERIOR || (xq + 0 >= 2 && xq + 0 < P.w - 2), vc1 = INTERIOR || (xq + 1 >= 2 && xq + 1 < P.w - 2);
+    const bool vc2 = INTERIOR || (xq + 2 >= 2 && xq + 2 < P.w - 2), vc3 = INTERIOR || (xq + 3 >= 2 && xq + 3 < P.w - 2);
+#pragma unroll
+    for (int a = 0; a < 5; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { rx[a][c] = 0.f; ry[a][c] = 0.f; }
+
+    float * pdx = P.dx + slot * P.stride; float * pdy = P.dy + slot * P.stride; float * pmag = P.mag + slot * P.stride;
+    uint8_t * pbin = P.bin + slot * P.stride;
+    const float * trow = tile + ty0 * K1_SW + lane * 4;
+
+#pragma unroll 1
+    for (int i = 0; i < RPT + 4; ++i, trow += K1_SW) {
+        // staged column k <-> image column x0 - 4 + k; this thread needs image columns xq-2 .. xq+5 = staged 4*lane+2 .. +9
+        const float4 q0 = *reinterpret_cast<const float4 *>(trow);
+        const float4 q1 = *reinterpret_cast<const float4 *>(trow + 4);
+        const float4 q2 = *reinterpret_cast<const float4 *>(trow + 8);
+        const float p[8] = {q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y};
+        float m[3][2][8];                       // m[a'][b'][j] = p[j] * |Hx(a',b')|
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            m[0][0][j] = __fmul_rn(p[j], LRB_K00); m[0][1][j] = __fmul_rn(p[j], LRB_K01);
+            m[1][0][j] = __fmul_rn(p[j], LRB_K10); m[1][1][j] = __fmul_rn(p[j], LRB_K11);
+            m[2][0][j] = __fmul_rn(p[j], LRB_K20); m[2][1][j] = __fmul_rn(p[j], LRB_K21);
+        }
+        // input row i is tap row a of output row i - a; rows outside [0, RPT) are skipped (warp-uniform branches)
+        if (i >= 4)                 tap_row<4>(m, rx[4], ry[4]);
+        if (i >= 3 && i < RPT + 3)  tap_row<3>(m, rx[3], ry[3]);
+        if (i >= 2 && i < RPT + 2)  tap_row<2>(m, rx[2], ry[2]);
+        if (i >= 1 && i < RPT + 1)  tap_row<1>(m, rx[1], ry[1]);
+        if (i < RPT)                tap_row<0>(m, rx[0], ry[0]);
+        // output row j = i - 4 is complete
+        if (i >= 4) {
+            const int y = y0 + ty0 + i - 4;
+            if (INTERIOR || (y < P.h && xq < P.wq)) {
+                const bool vy = INTERIOR || ((y >= 2) && (y < P.h - 2));
+                float4 odx, ody, omag; unsigned b0, b1, b2, b3;
+                finish_pixel<INTERIOR>(rx[4][0], ry[4][0], vy && vc0, odx.x, ody.x, omag.x, b0);
+                finish_pixel<INTERIOR>(rx[4][1], ry[4][1], vy && vc1, odx.y, ody.y, omag.y, b1);
+                finish_pixel<INTERIOR>(rx[4][2], ry[4][2], vy && vc2, odx.z, ody.z, omag.z, b2);
+                finish_pixel<INTERIOR>(rx[4][3], ry[4][3], vy && vc3, odx.w, ody.w, omag.w, b3);
+                const size_t o = (size_t)y * P.pitch + xq;
+                *reinterpret_cast<float4 *>(pdx + o) = odx;
+                *reinterpret_cast<float4 *>(pdy + o) = ody;
+                *reinterpret_cast<float4 *>(pmag + o) = omag;
+                *reinterpret_cast<unsigned *>(pbin + o) = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+                tmax = fmaxf(tmax, fmaxf(fmaxf(omag.x, omag.y), fmaxf(omag.z, omag.w)));
+            }
+        }
+        // every row moves on to its next tap row
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            rx[4][c] = rx[3][c]; rx[3][c] = rx[2][c]; rx[2][c] = rx[1][c]; rx[1][c] = rx[0][c];
+            ry[4][c] = ry[3][c]; ry[3][c] = ry[2][c]; ry[2][c] = ry[1][c]; ry[1][c] = ry[0][c];
+        }
+    }
+    return tmax;
+}
+
 template <int RPT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ctrl, int tma_x, int tma_y)
 {
     constexpr int TH = 8 * RPT, SH = TH + 4;
@@ -81,82 +186,10 @@ k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ct
     }
     mbar_wait(&bar, 0);
 
-    const int ty0 = warp * RPT;                 // first output row of this thread inside the tile
-    const int xq = x0 + lane * 4;               // first output column
-    float ax[RPT][4], ay[RPT][4];
-    float tmax = 0.0f;
-
-    float * pdx = P.dx + slot * P.stride; float * pdy = P.dy + slot * P.stride; float * pmag = P.mag + slot * P.stride;
-    uint8_t * pbin = P.bin + slot * P.stride;
-
-#pragma unroll
-    for (int i = 0; i < RPT + 4; ++i) {
-        // staged column k <-> image column x0 - 4 + k; this thread needs image columns xq-2 .. xq+5 = staged 4*lane+2 .. +9
-        const float4 q0 = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4]);
-        const float4 q1 = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4 + 4]);
-        const float4 q2 = *reinterpret_cast<const float4 *>(&tile[(ty0 + i) * K1_SW + lane * 4 + 8]);
-        const float p[8] = {q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y};
-        float m[3][2][8];                       // m[a'][b'][j] = p[j] * |Hx(a',b')|
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            m[0][0][j] = __fmul_rn(p[j], LRB_K00); m[0][1][j] = __fmul_rn(p[j], LRB_K01);
-            m[1][0][j] = __fmul_rn(p[j], LRB_K10); m[1][1][j] = __fmul_rn(p[j], LRB_K11);
-            m[2][0][j] = __fmul_rn(p[j], LRB_K20); m[2][1][j] = __fmul_rn(p[j], LRB_K21);
-        }
-#pragma unroll
-        for (int j = 0; j < RPT; ++j) {
-            const int a = i - j;                // tap row of input row i for output row j
-            if (a < 0 || a > 4) continue;
-            const int ar = a < 2 ? a : 4 - a;   // 0,1,2,1,0
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                // Hx row a: -K[ar][0], -K[ar][1], 0, +K[ar][1], +K[ar][0]
-                float sx = (a == 0) ? -m[ar][0][c] : __fsub_rn(ax[j][c], m[ar][0][c]);
-                sx = __fsub_rn(sx, m[ar][1][c + 1]);
-                sx = __fadd_rn(sx, m[ar][1][c + 3]);
-                sx = __fadd_rn(sx, m[ar][0][c + 4]);
-                ax[j][c] = sx;
-                // Hy row a: sign(a-2) * { K[0][ar], K[1][ar], K[2][ar], K[1][ar], K[0][ar] }, zero for a == 2
-                if (a != 2) {
-                    const int ac = ar;          // 0 or 1 here
-                    float sy;
-                    if (a < 2) {
-                        sy = (a == 0) ? -m[0][ac][c] : __fsub_rn(ay[j][c], m[0][ac][c]);
-                        sy = __fsub_rn(sy, m[1][ac][c + 1]);
-                        sy = __fsub_rn(sy, m[2][ac][c + 2]);
-                        sy = __fsub_rn(sy, m[1][ac][c + 3]);
-                        sy = __fsub_rn(sy, m[0][ac][c + 4]);
-                    } else {
-                        sy = __fadd_rn(ay[j][c], m[0][ac][c]);
-                        sy = __fadd_rn(sy, m[1][ac][c + 1]);
-                        sy = __fadd_rn(sy, m[2][ac][c + 2]);
-                        sy = __fadd_rn(sy, m[1][ac][c + 3]);
-                        sy = __fadd_rn(sy, m[0][ac][c + 4]);
-                    }
-                    ay[j][c] = sy;
-                }
-            }
-        }
-        // output row j = i - 4 is complete
-        if (i >= 4) {
-            const int j = i - 4;
-            const int y = y0 + ty0 + j;
-            if (y < P.h && xq < P.wq) {
-                const bool vy = (y >= 2) && (y < P.h - 2);
-                float4 odx, ody, omag; unsigned b0, b1, b2, b3;
-                finish_pixel(ax[j][0], ay[j][0], vy && (xq + 0 >= 2) && (xq + 0 < P.w - 2), odx.x, ody.x, omag.x, b0);
-                finish_pixel(ax[j][1], ay[j][1], vy && (xq + 1 >= 2) && (xq + 1 < P.w - 2), odx.y, ody.y, omag.y, b1);
-                finish_pixel(ax[j][2], ay[j][2], vy && (xq + 2 >= 2) && (xq + 2 < P.w - 2), odx.z, ody.z, omag.z, b2);
-                finish_pixel(ax[j][3], ay[j][3], vy && (xq + 3 >= 2) && (xq + 3 < P.w - 2), odx.w, ody.w, omag.w, b3);
-                const size_t o = (size_t)y * P.pitch + xq;
-                *reinterpret_cast<float4 *>(pdx + o) = odx;
-                *reinterpret_cast<float4 *>(pdy + o) = ody;
-                *reinterpret_cast<float4 *>(pmag + o) = omag;
-                *reinterpret_cast<unsigned *>(pbin + o) = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
-                tmax = fmaxf(tmax, fmaxf(fmaxf(omag.x, omag.y), fmaxf(omag.z, omag.w)));
-            }
-        }
-    }
+    // tiles that touch neither the 2-px border nor the right / bottom edge skip all validity logic
+    const bool interior = (x0 >= 2) && (x0 + K1_TW <= P.w - 2) && (y0 >= 2) && (y0 + TH <= P.h - 2);
+    const float tmax = interior ? compute_strip<RPT, true>(tile, P, slot, x0, y0, lane, warp)
+                                : compute_strip<RPT, false>(tile, P, slot, x0, y0, lane, warp);
 
     // frame maximum of mag: mag >= 0, so the uint order of the bit patterns is the float order
     unsigned um = __float_as_uint(tmax);
