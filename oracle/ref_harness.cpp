@@ -65,8 +65,10 @@ void ref_set_seed(unsigned s) { oracle_ref_seed_value = s; }
  * In a fresh process the plane comes from a fresh (zeroed) mmap, i.e. bin 0, which is what the restatement defines.
  * Pinning the mmap threshold makes every allocation >= 16 KiB a fresh zeroed mapping, so the *unmodified* reference
  * behaves like that on every call instead of only on the first one. Used for the parity oracle only, never for the
- * timed baseline. */
-void ref_set_deterministic_malloc() { mallopt(M_MMAP_THRESHOLD, 16384); }
+ * timed baseline.  Smaller blocks (which malloc recycles dirty) are covered by M_PERTURB = 0xff: glibc then fills
+ * every malloc'ed block with the complement, i.e. zero bytes - without it the compiled reference's result was seen
+ * to depend on what had been freed before the call (one segment more or less after other tests had run). */
+void ref_set_deterministic_malloc() { mallopt(M_MMAP_THRESHOLD, 16384); mallopt(M_PERTURB, 0xff); }
 
 /* 5x5 taps, row-major, dir_x != 0 -> Hx */
 void ref_gauss_deriv_kernel(int dir_x, float * out25)
