@@ -67,7 +67,7 @@ struct FrameCtrl {
     int flood_done;            // set by the serial fallback
     int fit_done;              // components selected and fitted on final floods
     int win_lo, win_hi;        // flood window: ranks processed by the current round
-    int pool_cursor;           // next free chunk of the pixel-list pool
+    int pool_cursor;           // next free word of the pixel-list pool
     int win_live, win_first, win_blocks;   // commit-kernel scratch (live seeds left in the window, lowest of them, blocks done)
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
     // grouping state
@@ -121,7 +121,9 @@ struct Comps {                  // per slot
     unsigned * px;              // pixel raster indices in the reference's BFS order
     float * val;                // G_bin at those pixels
     float * seg;                // raw LineSegment records (7 x 4 bytes each)
-    unsigned * pool; int cap_pool;   // per-round pixel lists of the tentative floods (32-word chunks)
+    unsigned * pool; int cap_pool;   // per-round pixel lists of the tentative floods (contiguous, one atomicAdd per list)
+    // tile tables in global memory for floods that outgrow the shared-memory table (k4_flood.cu); shared by all slots
+    unsigned * big; int * big_lock; int big_slots, big_cap; size_t big_bytes;
 };
 
 struct Lines {                  // per slot: filtered segments and the pencil model built on them

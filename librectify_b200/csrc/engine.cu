@@ -78,6 +78,7 @@ int make_tmap(CUtensorMap * m, CUtensorMapDataType dt, int esize, const void * b
 constexpr int kT = kRansacIter;
 constexpr int kLinesHead = 4096;       // segments per slot copied back together with the control block
 constexpr int kInitialRounds = 16;
+constexpr int kBigSlots = 64;          // concurrent long floods (global-memory tile tables) per engine
 
 } // namespace
 
@@ -143,6 +144,8 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     const size_t cap_px = npx;
     const size_t cap_pool = (2 * npx + 65536) / 32 * 32;
     const int cap_lines = cap_comp;
+    const int big_cap = (int)std::min<size_t>(((size_t)(w + 31) / 32) * ((size_t)(h + 31) / 32), 4096);   // tiles per long flood
+    const size_t big_bytes = ((size_t)big_cap * (256 + 12) + 255) / 256 * 256;
     auto layout = [&](char * base) {
         char * p = base;
         e->ws_img_raw = carve<float>(p, plane * G); e->ws_img = e->ws_img_raw + org;
@@ -163,6 +166,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
         e->K.px = carve<unsigned>(p, cap_px * G); e->K.val = carve<float>(p, cap_px * G);
         e->K.seg = carve<float>(p, (size_t)cap_comp * 7 * G);
         e->K.pool = carve<unsigned>(p, cap_pool * G);
+        e->K.big = carve<unsigned>(p, big_bytes / 4 * kBigSlots); e->K.big_lock = carve<int>(p, kBigSlots);
         e->L.seg = carve<float>(p, (size_t)cap_lines * 7 * G); e->L.h = carve<float>(p, (size_t)cap_lines * 3 * G);
         e->L.anchor = carve<float>(p, (size_t)cap_lines * 2 * G); e->L.dir = carve<float>(p, (size_t)cap_lines * 2 * G);
         e->L.len = carve<float>(p, (size_t)cap_lines * G);
@@ -185,6 +189,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     e->P.w = w; e->P.h = h; e->P.pitch = pitch; e->P.stride = plane; e->P.wq = (w + 3) / 4 * 4;
     e->P.img = e->ws_img; e->P.img_stride = plane; e->P.img_pitch = pitch;
     e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->K.cap_pool = (int)std::min<size_t>(cap_pool, 0x7fffffe0); e->L.cap = cap_lines;
+    e->K.big_slots = kBigSlots; e->K.big_cap = big_cap; e->K.big_bytes = big_bytes;
     CK(cudaMemsetAsync(e->arena, 0, bytes, e->st));
     launch_fill_u32(e->owner_raw, plane * G, kOwnerInit, e->st);
     e->next_epoch = 0xFE;

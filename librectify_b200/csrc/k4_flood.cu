@@ -16,11 +16,11 @@
 // commits — and by the time their turn comes most of them lie inside a committed region (seeds along one line are
 // dominated by the line's strongest seed) and are dropped without ever flooding, as in the sequential algorithm.
 //
-// Latency is what bounds this stage (a 2000-px line is a 1000-level BFS), so the exploration loop touches only data
-// that is constant during a round — mask8, dx, dy and the visited mask — through the non-coherent L1 path; the owner
-// stamps are write-only here and are inspected by the verify kernel.  owner word = [epoch | rank]; epochs DEcrease from
-// round to round and frame to frame, so a newer stamp always wins over stale ones and the plane is re-initialised only
-// when the epoch field wraps.
+// Latency is what bounds this stage, so a tentative flood works on 32x32 tiles held as bitmaps (see below): memory
+// latency is paid per tile, not per BFS level, and the exploration touches only data that is constant during a round —
+// mask8, dx, dy and the visited mask — through the non-coherent path; the owner stamps are write-only here and are
+// inspected by the verify kernel.  owner word = [epoch | rank]; epochs DEcrease from round to round and frame to frame,
+// so a newer stamp always wins over stale ones and the plane is re-initialised only when the epoch field wraps.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -29,28 +29,209 @@ namespace lrb {
 namespace {
 
 constexpr int FL_WARPS = 4;
-constexpr int FL_QCAP  = 1024;    // BFS ring per warp: must hold three consecutive BFS levels (frontier-, not region-bound)
+constexpr int FT_SMALL = 16;      // tiles a flood may touch before it moves from shared memory to a global-memory table
 
-// reference src/filter.cpp:113-116 neighbour order (dr, dc)
+// reference src/filter.cpp:113-116 neighbour order (dr, dc) — used by the serial fallback below
 static __device__ __constant__ const int kDr[8] = {0, 0, 1, -1, -1, -1, 1, 1};
 static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
 
-// Pixel lists live in a per-frame pool of 32-word chunks: word 0 = index of the next chunk + 1 (0: none), words 1..31 =
-// pixels as (row << 16 | col).  The pool is recycled every round.
-__device__ __forceinline__ int pool_alloc(FrameCtrl & C, int cap_chunks)
+// ---- tile-bitmap flood ----------------------------------------------------------------------------------------------
+// The frame is cut into aligned 32x32 tiles.  For one seed a tile is two 32-word bitmaps, lane = row, bit = column:
+//   E  eligible pixels: interior (filter.cpp:101-107), dilated bin mask bit b set, not visited, G_b(p) > thr (filter.cpp:131)
+//   R  pixels reached so far
+// A flood step inside a tile is pure register work: R <- E & dilate3x3(R) with two shuffles for the rows above/below,
+// iterated to a fixed point; only what spills over the tile edge is handed to the (up to eight) neighbouring tiles, whose
+// E is computed when they are first touched.  Memory latency is paid once per tile (two dependent rounds of wide loads)
+// instead of once per BFS level, and the region comes out as the same set the sequential flood reaches — the order in
+// which a connected set is discovered does not change the set.
+struct FloodCtx {
+    const uint8_t * mask8; const uint8_t * vis; const float * dx; const float * dy;
+    int w, h, pitch, b;
+    float thr, sb, cb;
+};
+
+// table of touched tiles: ids (ty << 16 | tx), dirty flags, a ring of dirty entries, and the bitmaps [entry][E 0..31 | R 32..63]
+struct TileTab { int * ids; int * dirty; int * ring; unsigned * er; int cap; };
+
+// 32 bytes (two 16-byte loads) -> 32 bits: bit i = bit `sh` of byte i
+__device__ __forceinline__ unsigned bits_of_bytes(const uint4 & a, const uint4 & b, int sh)
 {
-    int c = 0;
-    if ((threadIdx.x & 31) == 0) c = atomicAdd(&C.pool_cursor, 1);
-    c = __shfl_sync(0xffffffffu, c, 0);
-    return c < cap_chunks ? c : -1;
+#define LRB_F(wd) (((((wd) >> sh) & 0x01010101u) * 0x01020408u) >> 24)
+    return LRB_F(a.x) | (LRB_F(a.y) << 4) | (LRB_F(a.z) << 8) | (LRB_F(a.w) << 12) |
+           (LRB_F(b.x) << 16) | (LRB_F(b.y) << 20) | (LRB_F(b.z) << 24) | (LRB_F(b.w) << 28);
+#undef LRB_F
 }
 
-// one tentative flood of seed `rank` by one warp: level-synchronous BFS, up to four pixels of the current level are
-// expanded against their eight neighbours per step (one candidate per lane).  The ring keeps every pixel pushed for the
-// previous, the current and the next level; a neighbour of a level-L pixel lies in level L-1, L or L+1, so "already
-// reached" is a search in that window.
+// eligibility bitmap of tile (ty, tx) for this seed; lane = row of the tile
+__device__ __forceinline__ unsigned tile_eligible(const FloodCtx & X, int ty, int tx, int lane)
+{
+    const int y = ty * 32 + lane, x0 = tx * 32;
+    unsigned cand = 0;
+    if (y >= 1 && y < X.h - 1) {
+        const size_t ro = (size_t)y * X.pitch + x0;
+        const uint4 * pm = reinterpret_cast<const uint4 *>(X.mask8 + ro);
+        const uint4 * pv = reinterpret_cast<const uint4 *>(X.vis + ro);
+        const bool second = x0 + 16 < X.pitch;
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        const uint4 m0 = __ldg(pm), v0 = __ldg(pv);
+        const uint4 m1 = second ? __ldg(pm + 1) : z, v1 = second ? __ldg(pv + 1) : z;
+        unsigned cols = 0xFFFFFFFFu;                                        // columns 1 .. w-2 only
+        if (x0 == 0) cols &= ~1u;
+        const int last = X.w - 1 - x0;                                      // first column of this tile that is NOT interior
+        if (last < 32) cols &= (last <= 0) ? 0u : ((1u << last) - 1u);
+        cand = bits_of_bytes(m0, m1, X.b) & ~bits_of_bytes(v0, v1, 0) & cols;
+    }
+    unsigned E = 0;
+    unsigned rows = __ballot_sync(0xffffffffu, cand != 0);
+    while (rows) {                                                          // two candidate rows per trip: loads of both in flight
+        const int r0 = __ffs(rows) - 1; rows &= rows - 1;
+        const int r1 = rows ? __ffs(rows) - 1 : -1; if (rows) rows &= rows - 1;
+        const unsigned c0 = __shfl_sync(0xffffffffu, cand, r0);
+        const unsigned c1 = __shfl_sync(0xffffffffu, cand, r1 < 0 ? 0 : r1);
+        const bool p0 = (c0 >> lane) & 1u, p1 = (r1 >= 0) && ((c1 >> lane) & 1u);
+        float gx0 = 0.f, gy0 = 0.f, gx1 = 0.f, gy1 = 0.f;
+        if (p0) { const size_t po = (size_t)(ty * 32 + r0) * X.pitch + tx * 32 + lane; gx0 = __ldg(X.dx + po); gy0 = __ldg(X.dy + po); }
+        if (p1) { const size_t po = (size_t)(ty * 32 + r1) * X.pitch + tx * 32 + lane; gx1 = __ldg(X.dx + po); gy1 = __ldg(X.dy + po); }
+        const float g0 = fabsf(__fadd_rn(__fmul_rn(gx0, X.sb), __fmul_rn(gy0, X.cb)));
+        const float g1 = fabsf(__fadd_rn(__fmul_rn(gx1, X.sb), __fmul_rn(gy1, X.cb)));
+        const unsigned e0 = __ballot_sync(0xffffffffu, p0 && g0 > X.thr);
+        const unsigned e1 = __ballot_sync(0xffffffffu, p1 && g1 > X.thr);
+        if (lane == r0) E = e0;
+        if (lane == r1) E = e1;
+    }
+    return E;
+}
+
+__device__ __forceinline__ int tab_find(const TileTab & T, int n_ent, int id, int lane)
+{
+    for (int base = 0; base < n_ent; base += 32) {
+        const int i = base + lane;
+        const unsigned m = __ballot_sync(0xffffffffu, i < n_ent && T.ids[i] == id);
+        if (m) return base + __ffs(m) - 1;
+    }
+    return -1;
+}
+
+// Tentative region of one seed by one warp.  Returns the pixel count, or -1 when the table is full.
+// On success the bitmaps of the n_ent touched tiles are in T (R part).
+__device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T, int sr, int sc, int & n_ent_out)
+{
+    const int lane = threadIdx.x & 31;
+    const int tiles_x = (X.w + 31) >> 5, tiles_y = (X.h + 31) >> 5;
+    int n_ent = 1, q_head = 0, q_tail = 1;
+    {   // the seed's tile; the seed itself is accepted unconditionally (filter.cpp:119-122)
+        const int ty = sr >> 5, tx = sc >> 5;
+        unsigned E = tile_eligible(X, ty, tx, lane);
+        const unsigned sbit = (lane == (sr & 31)) ? (1u << (sc & 31)) : 0u;
+        E |= sbit;
+        T.er[lane] = E; T.er[32 + lane] = sbit;
+        if (lane == 0) { T.ids[0] = (ty << 16) | tx; T.dirty[0] = 1; T.ring[0] = 0; }
+        __syncwarp();
+    }
+    while (q_head < q_tail) {
+        const int e = T.ring[q_head % T.cap]; ++q_head;
+        const int id = T.ids[e];
+        const int ty = id >> 16, tx = id & 0xFFFF;
+        const unsigned E = T.er[e * 64 + lane];
+        unsigned R = T.er[e * 64 + 32 + lane];
+        __syncwarp();
+        if (lane == 0) T.dirty[e] = 0;
+        unsigned hz;
+        while (true) {                                                      // fixed point of R <- E & dilate(R)
+            hz = R | (R << 1) | (R >> 1);
+            unsigned up = __shfl_up_sync(0xffffffffu, hz, 1), dn = __shfl_down_sync(0xffffffffu, hz, 1);
+            if (lane == 0) up = 0u;
+            if (lane == 31) dn = 0u;
+            const unsigned Rn = R | (E & (hz | up | dn));
+            const bool ch = __any_sync(0xffffffffu, Rn != R);
+            R = Rn;
+            if (!ch) break;
+        }
+        T.er[e * 64 + 32 + lane] = R;
+        __syncwarp();
+        // what reaches over the tile edge: left/right columns, first/last row
+        const bool edge = __any_sync(0xffffffffu, (R & 0x80000001u) != 0u || ((lane == 0 || lane == 31) && R != 0u));
+        if (!edge) continue;
+        const unsigned hr = R >> 31, hl = (R & 1u) << 31;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int dy = (k < 3) ? -1 : (k < 5 ? 0 : 1);
+            const int dxk = (k < 3) ? k - 1 : (k < 5 ? (k == 3 ? -1 : 1) : k - 6);
+            const unsigned src = dxk == 0 ? hz : (dxk > 0 ? hr : hl);
+            unsigned spill;
+            if (dy == 0) {
+                unsigned up = __shfl_up_sync(0xffffffffu, src, 1), dn = __shfl_down_sync(0xffffffffu, src, 1);
+                if (lane == 0) up = 0u;
+                if (lane == 31) dn = 0u;
+                spill = src | up | dn;
+            } else if (dy > 0) {
+                const unsigned v = __shfl_sync(0xffffffffu, src, 31);
+                spill = lane == 0 ? v : 0u;
+            } else {
+                const unsigned v = __shfl_sync(0xffffffffu, src, 0);
+                spill = lane == 31 ? v : 0u;
+            }
+            if (!__any_sync(0xffffffffu, spill != 0u)) continue;
+            const int ny = ty + dy, nx = tx + dxk;
+            if (ny < 0 || nx < 0 || ny >= tiles_y || nx >= tiles_x) continue;
+            const int nid = (ny << 16) | nx;
+            int ne = tab_find(T, n_ent, nid, lane);
+            if (ne < 0) {
+                const unsigned En = tile_eligible(X, ny, nx, lane);
+                if (!__any_sync(0xffffffffu, (En & spill) != 0u)) continue;       // nothing to reach there: do not spend an entry
+                if (n_ent >= T.cap) { n_ent_out = n_ent; return -1; }
+                ne = n_ent++;
+                T.er[ne * 64 + lane] = En; T.er[ne * 64 + 32 + lane] = 0u;
+                if (lane == 0) { T.ids[ne] = nid; T.dirty[ne] = 0; }
+                __syncwarp();
+            }
+            const unsigned nb = spill & T.er[ne * 64 + lane] & ~T.er[ne * 64 + 32 + lane];
+            if (__any_sync(0xffffffffu, nb != 0u)) {
+                const int was_dirty = T.dirty[ne];                            // same word for every lane
+                __syncwarp();
+                T.er[ne * 64 + 32 + lane] |= nb;
+                if (!was_dirty) {
+                    if (lane == 0) { T.dirty[ne] = 1; T.ring[q_tail % T.cap] = ne; }
+                    ++q_tail;
+                }
+                __syncwarp();
+            }
+        }
+    }
+    int cnt = 0;
+    for (int e = 0; e < n_ent; ++e) cnt += __popc(T.er[e * 64 + 32 + lane]);
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
+    n_ent_out = n_ent;
+    return cnt;
+}
+
+// stamp the region (fire-and-forget atomicMin(owner, epoch:rank)) and write its pixel list; row by row, lane = column
+__device__ __forceinline__ void emit_region(const Planes & P, unsigned * owner, const TileTab & T, int n_ent, unsigned key, unsigned * list)
+{
+    const int lane = threadIdx.x & 31;
+    int off = 0;
+    for (int e = 0; e < n_ent; ++e) {
+        const unsigned R = T.er[e * 64 + 32 + lane];
+        const int id = T.ids[e];
+        const int y0 = (id >> 16) * 32, x = (id & 0xFFFF) * 32 + lane;
+        unsigned rows = __ballot_sync(0xffffffffu, R != 0u);
+        while (rows) {
+            const int r = __ffs(rows) - 1; rows &= rows - 1;
+            const unsigned m = __shfl_sync(0xffffffffu, R, r);
+            if ((m >> lane) & 1u) {
+                const int y = y0 + r;
+                atomicMin(owner + (size_t)y * P.pitch + x, key);
+                list[off + __popc(m & ((1u << lane) - 1u))] = ((unsigned)y << 16) | (unsigned)x;
+            }
+            off += __popc(m);
+        }
+    }
+}
+
+// one tentative flood of seed `rank` by one warp
 __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl & C, int slot, int rank,
-                                          unsigned epoch, unsigned * q)
+                                          unsigned epoch, const TileTab & Tsm)
 {
     const int lane = threadIdx.x & 31;
     const size_t so = (size_t)slot * S.cap;
@@ -58,88 +239,59 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
 
     const size_t pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
-    const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
-    const uint8_t * mask8 = P.mask8 + pbase; const uint8_t * vis = P.vis + pbase;
-    unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
-    const int cap_chunks = K.cap_pool / 32;
+    FloodCtx X;
+    X.dx = P.dx + pbase; X.dy = P.dy + pbase; X.mask8 = P.mask8 + pbase; X.vis = P.vis + pbase;
+    X.w = P.w; X.h = P.h; X.pitch = P.pitch;
 
     const unsigned key = (epoch << 24) | (unsigned)rank;
     const unsigned spx = S.idx[so + rank];
     const int sr = spx / P.w, sc = spx - sr * P.w;
-    const size_t spo = (size_t)sr * P.pitch + sc;
-    if (__ldg(vis + spo)) {                                   // line_detector.cpp:103: seed already swallowed
+    if (__ldg(X.vis + (size_t)sr * P.pitch + sc)) {               // line_detector.cpp:103: seed already swallowed
         if (lane == 0) S.status[so + rank] = kStatusDropped;
         return;
     }
-    const int b = S.bin[so + rank];
-    const float thr = S.thr[so + rank];
-    const float sb = kSin[b], cb = kCos[b];
+    X.b = S.bin[so + rank];
+    X.thr = S.thr[so + rank];
+    X.sb = kSin[X.b]; X.cb = kCos[X.b];
 
-    // the seed itself: G_b(seed) > 0.75 G_b(seed) holds by construction (filter.cpp:119-131)
-    if (lane == 0) { atomicMin(owner + spo, key); q[0] = ((unsigned)sr << 16) | (unsigned)sc; }
+    int n_ent = 0;
+    int size = flood_tiles(X, Tsm, sr, sc, n_ent);
+    TileTab T = Tsm;
+    int big = -1;
+    if (size < 0) {                                               // a long region: redo it on a table in global memory
+        if (lane == 0) {
+            unsigned h = (unsigned)rank * 2654435761u + blockIdx.x;
+            while (big < 0) {
+                for (int t = 0; t < K.big_slots && big < 0; ++t) {
+                    const int i = (int)((h + t) % (unsigned)K.big_slots);
+                    if (atomicCAS(K.big_lock + i, 0, 1) == 0) big = i;
+                }
+                if (big < 0) __nanosleep(500);
+            }
+            __threadfence();
+        }
+        big = __shfl_sync(0xffffffffu, big, 0);
+        char * base = reinterpret_cast<char *>(K.big) + (size_t)big * K.big_bytes;
+        T.cap = K.big_cap;
+        T.er = reinterpret_cast<unsigned *>(base);
+        T.ids = reinterpret_cast<int *>(base + (size_t)K.big_cap * 256);
+        T.dirty = T.ids + K.big_cap; T.ring = T.dirty + K.big_cap;
+        size = flood_tiles(X, T, sr, sc, n_ent);
+    }
+    bool overflow = size < 0;
+    int off = 0;
+    if (!overflow) {
+        if (lane == 0) off = atomicAdd(&C.pool_cursor, size);
+        off = __shfl_sync(0xffffffffu, off, 0);
+        if (off + size > K.cap_pool) overflow = true;
+        else emit_region(P, owner, T, n_ent, key, K.pool + (size_t)slot * K.cap_pool + off);
+    }
     __syncwarp();
-    int head = 0, tail = 1;                 // absolute positions in the push sequence; ring index = pos & (FL_QCAP-1)
-    int s_prev = 0, s_cur = 0, s_next = 1;  // first push of the previous / current / next BFS level
-    int flushed = 0, first_chunk = -1, last_chunk = -1;
-    bool overflow = false;
-
-    while (head < tail) {
-        if (head >= s_next) { s_prev = s_cur; s_cur = s_next; s_next = tail; }
-        const int cnt = min(4, s_next - head);                             // a step never straddles two levels
-        const int pslot = lane >> 3, k = lane & 7;
-        const bool act = pslot < cnt;
-        const unsigned prc = q[(head + (act ? pslot : 0)) & (FL_QCAP - 1)];
-        head += cnt;
-        const int r = (int)(prc >> 16) + kDr[k], c = (int)(prc & 0xFFFFu) + kDc[k];
-        bool elig = act && r >= 1 && r < P.h - 1 && c >= 1 && c < P.w - 1;      // filter.cpp:101-107: border is visited
-        const size_t po = (size_t)(elig ? r : 0) * P.pitch + (elig ? c : 0);
-        if (elig) {
-            const unsigned m8 = __ldg(mask8 + po), v = __ldg(vis + po);
-            const float gx = __ldg(dx + po), gy = __ldg(dy + po);
-            const float g = fabsf(__fadd_rn(__fmul_rn(gx, sb), __fmul_rn(gy, cb)));
-            elig = ((m8 >> b) & 1u) && !v && (g > thr);                         // dilated bin mask, not visited, filter.cpp:131
-        }
-        const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
-        if (elig) {                                                             // reached before (previous / this / next level)?
-            bool seen = false;
-            for (int i = s_prev; i < tail; ++i) seen |= (q[i & (FL_QCAP - 1)] == rcq);
-            elig = !seen;
-        }
-        // the same pixel may be reached from several parents in one step: lowest lane handles it
-        const unsigned long long mkey = elig ? (unsigned long long)rcq : ((1ull << 40) | (unsigned)lane);
-        const unsigned same = __match_any_sync(0xffffffffu, mkey);
-        const bool reached = elig && (lane == __ffs(same) - 1);
-        if (reached) atomicMin(owner + po, key);                                // result unused: a reduction, off the critical path
-        const unsigned pm = __ballot_sync(0xffffffffu, reached);
-        const int np = __popc(pm);
-        if (tail + np - min(s_prev, flushed) > FL_QCAP) { overflow = true; break; }   // the ring must keep three levels + unflushed pixels
-        if (reached) q[(tail + __popc(pm & ((1u << lane) - 1))) & (FL_QCAP - 1)] = rcq;
-        tail += np;
-        __syncwarp();
-        // spill completed groups of 31 pixels to the pool
-        while (tail - flushed >= 31) {
-            const int ch = pool_alloc(C, cap_chunks);
-            if (ch < 0) { overflow = true; break; }
-            pool[(size_t)ch * 32 + lane] = lane ? q[(flushed + lane - 1) & (FL_QCAP - 1)] : 0u;
-            if (lane == 0 && last_chunk >= 0) pool[(size_t)last_chunk * 32] = (unsigned)ch + 1u;
-            if (first_chunk < 0) first_chunk = ch;
-            last_chunk = ch; flushed += 31;
-        }
-        if (overflow) break;
-    }
-    if (!overflow && tail > flushed) {                                          // the last, partial chunk
-        const int ch = pool_alloc(C, cap_chunks);
-        if (ch < 0) overflow = true;
-        else {
-            pool[(size_t)ch * 32 + lane] = (lane && flushed + lane - 1 < tail) ? q[(flushed + lane - 1) & (FL_QCAP - 1)] : 0u;
-            if (lane == 0 && last_chunk >= 0) pool[(size_t)last_chunk * 32] = (unsigned)ch + 1u;
-            if (first_chunk < 0) first_chunk = ch;
-        }
-    }
+    if (big >= 0 && lane == 0) { __threadfence(); atomicExch(K.big_lock + big, 0); }
     if (lane == 0) {
         if (overflow) C.flood_overflow = 1;
-        S.size[so + rank] = overflow ? -1 : tail;
-        S.list_head[so + rank] = first_chunk;
+        S.size[so + rank] = overflow ? -1 : size;
+        S.list_head[so + rank] = off;
     }
     __syncwarp();
 }
@@ -147,15 +299,18 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
 __global__ void __launch_bounds__(FL_WARPS * 32)
 k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first)
 {
-    __shared__ unsigned q[FL_WARPS][FL_QCAP];
+    __shared__ unsigned s_er[FL_WARPS][FT_SMALL * 64];
+    __shared__ int s_ids[FL_WARPS][FT_SMALL * 3];
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
     const int lo = C.win_lo, hi = C.win_hi;
     const int warp = threadIdx.x >> 5;
     const unsigned epoch = epoch_first - (unsigned)round;
+    TileTab T;
+    T.er = s_er[warp]; T.ids = s_ids[warp]; T.dirty = T.ids + FT_SMALL; T.ring = T.dirty + FT_SMALL; T.cap = FT_SMALL;
     for (int rank = lo + blockIdx.x * FL_WARPS + warp; rank < hi; rank += gridDim.x * FL_WARPS)
-        flood_one(P, S, K, C, slot, rank, epoch, q[warp]);
+        flood_one(P, S, K, C, slot, rank, epoch, T);
 }
 
 // verify + commit + mark visited, one warp per window seed; the last block to finish moves the window
@@ -180,25 +335,18 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         const unsigned key = (epoch << 24) | (unsigned)rank;
         const int size = S.size[so + rank];
         // pass 1: is every pixel still stamped with this seed's key?
+        const unsigned * list = pool + S.list_head[so + rank];
         bool mine = true;
-        int left = size;
-        for (int ch = S.list_head[so + rank]; ch >= 0 && left > 0; ) {
-            const unsigned w = __ldcg(pool + (size_t)ch * 32 + lane);
-            const int here = min(left, 31);
-            if (lane >= 1 && lane <= here) mine &= (__ldcg(owner + (size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)) == key);
-            left -= here;
-            ch = (int)__shfl_sync(0xffffffffu, w, 0) - 1;
+        for (int i = lane; i < size; i += 32) {
+            const unsigned w = __ldcg(list + i);
+            mine &= (__ldcg(owner + (size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)) == key);
         }
         mine = __all_sync(0xffffffffu, mine);
         if (!mine) { ++live; first = min(first, rank); continue; }
         // pass 2: the region is final — it becomes part of the visited mask (whether or not it is kept later)
-        left = size;
-        for (int ch = S.list_head[so + rank]; ch >= 0 && left > 0; ) {
-            const unsigned w = __ldcg(pool + (size_t)ch * 32 + lane);
-            const int here = min(left, 31);
-            if (lane >= 1 && lane <= here) vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
-            left -= here;
-            ch = (int)__shfl_sync(0xffffffffu, w, 0) - 1;
+        for (int i = lane; i < size; i += 32) {
+            const unsigned w = __ldcg(list + i);
+            vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
         }
         if (lane == 0) S.status[so + rank] = key;
     }
