@@ -82,7 +82,10 @@ struct FrameCtrl {
     int stream_overflow;
     int samp_done;                         // samples already emitted by the parallel sampler (the sequential walk finishes the rest)
     float bbox[4], cx, cy, scale;
-    int pad_[8];
+    int dbg_floods, dbg_big, dbg_tiles, dbg_px, dbg_maxpx, dbg_commit_px;   // flood statistics (LRB_DEBUG_STATS)
+    unsigned long long dbg_maxdur;   // (ns << 24) | px of the slowest flood
+    unsigned long long dbg_sumdur;
+    int dbg_slow[4];
 };
 
 // ---- views passed to kernels by value -----------------------------------------------------------------------------
@@ -101,6 +104,7 @@ struct Planes {                 // one frame slot = one set of planes; slot s li
 
 struct Seeds {                  // per slot: s * cap
     int cap;
+    int win_min, win_div;                     // seeds flooded per round: max(win_min, n_seeds / win_div)
     unsigned * us_mag; unsigned * us_idx;     // unsorted (emission order)
     unsigned * b_mag;  unsigned * b_idx;      // bucketed
     unsigned * idx;                           // sorted by (mag desc, raster idx asc): rank -> pixel

@@ -142,7 +142,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     const int cap_seeds = (int)std::min<size_t>(npx / e->seed_div + 1024, (1u << 24) - 1);
     const int cap_comp = (int)(npx / 6 + 16);
     const size_t cap_px = npx;
-    const size_t cap_pool = (2 * npx + 65536) / 32 * 32;
+    const size_t cap_pool = (3 * npx + 65536 + (size_t)148 * 24 * 256) / 32 * 32;
     const int cap_lines = cap_comp;
     const int big_cap = (int)std::min<size_t>(((size_t)(w + 31) / 32) * ((size_t)(h + 31) / 32), 4096);   // tiles per long flood
     const size_t big_bytes = ((size_t)big_cap * (256 + 12) + 255) / 256 * 256;
@@ -188,6 +188,9 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     e->w = w; e->h = h; e->pitch = pitch; e->plane = plane;
     e->P.w = w; e->P.h = h; e->P.pitch = pitch; e->P.stride = plane; e->P.wq = (w + 3) / 4 * 4;
     e->P.img = e->ws_img; e->P.img_stride = plane; e->P.img_pitch = pitch;
+    e->S.win_min = kFloodWindowMin; e->S.win_div = kFloodWindowDiv;
+    if (const char * v = getenv("LRB_WINDOW_MIN")) e->S.win_min = std::max(1, atoi(v));
+    if (const char * v = getenv("LRB_WINDOW_DIV")) e->S.win_div = std::max(1, atoi(v));
     e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->K.cap_pool = (int)std::min<size_t>(cap_pool, 0x7fffffe0); e->L.cap = cap_lines;
     e->K.big_slots = kBigSlots; e->K.big_cap = big_cap; e->K.big_bytes = big_bytes;
     CK(cudaMemsetAsync(e->arena, 0, bytes, e->st));
@@ -372,6 +375,8 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         if (int r = readback(e, n, quiet)) { e->prof = prof_saved; return r; }
         CK(cudaGetLastError());
     }
+    if (getenv("LRB_DEBUG_STATS")) for (int i = 0; i < n; ++i) { const FrameCtrl & C = e->h_ctrl[i];
+        fprintf(stderr, "[lrb] slot %d: seeds %d rounds %d floods %d big %d tiles %d px %d maxpx %d committed px %d comps %d slowest flood %.1f us (%d px; visits %d iters %d evals %d tiles %d) mean %.2f us\n", i, C.n_seeds, C.rounds_run, C.dbg_floods, C.dbg_big, C.dbg_tiles, C.dbg_px, C.dbg_maxpx, C.dbg_commit_px, C.n_comp, (C.dbg_maxdur >> 24) * 1e-3, (int)(C.dbg_maxdur & 0xFFFFFF), C.dbg_slow[0], C.dbg_slow[1], C.dbg_slow[2], C.dbg_slow[3], C.dbg_sumdur * 1e-3 / std::max(1, C.dbg_floods)); }
     e->prof = prof_saved;
     e->next_epoch = epoch_first - (unsigned)rounds - 2;
     if (std::any_of(e->last_fallback.begin(), e->last_fallback.end(), [](int v) { return v != 0; })) e->next_epoch = 0;   // force a re-init

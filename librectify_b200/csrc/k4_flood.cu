@@ -29,6 +29,7 @@ namespace lrb {
 namespace {
 
 constexpr int FL_WARPS = 4;
+constexpr int kPoolGranule = 256;  // list space a warp takes from the pool at a time (words)
 constexpr int FT_SMALL = 16;      // tiles a flood may touch before it moves from shared memory to a global-memory table
 
 // reference src/filter.cpp:113-116 neighbour order (dr, dc) — used by the serial fallback below
@@ -36,7 +37,7 @@ static __device__ __constant__ const int kDr[8] = {0, 0, 1, -1, -1, -1, 1, 1};
 static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
 
 // ---- tile-bitmap flood ----------------------------------------------------------------------------------------------
-// The frame is cut into aligned 32x32 tiles.  For one seed a tile is two 32-word bitmaps, lane = row, bit = column:
+// The plane is cut into 32x32 tiles (a grid anchored at the seed).  For one seed a tile is two 32-word bitmaps, lane = row, bit = column:
 //   E  eligible pixels: interior (filter.cpp:101-107), dilated bin mask bit b set, not visited, G_b(p) > thr (filter.cpp:131)
 //   R  pixels reached so far
 // A flood step inside a tile is pure register work: R <- E & dilate3x3(R) with two shuffles for the rows above/below,
@@ -52,6 +53,10 @@ struct FloodCtx {
 
 // table of touched tiles: ids (ty << 16 | tx), dirty flags, a ring of dirty entries, and the bitmaps [entry][E 0..31 | R 32..63]
 struct TileTab { int * ids; int * dirty; int * ring; unsigned * er; int cap; };
+constexpr int kTileBias = 4096;
+__device__ __forceinline__ int tile_id(int ty, int tx) { return ((ty + kTileBias) << 16) | (tx + kTileBias); }
+__device__ __forceinline__ int tile_origin_y(int sr) { return sr - 16; }
+__device__ __forceinline__ int tile_origin_x(int sc) { return ((sc - 8) >> 4) << 4; }      // seed column lands in [8, 24)
 
 // 32 bytes (two 16-byte loads) -> 32 bits: bit i = bit `sh` of byte i
 __device__ __forceinline__ unsigned bits_of_bytes(const uint4 & a, const uint4 & b, int sh)
@@ -62,44 +67,54 @@ __device__ __forceinline__ unsigned bits_of_bytes(const uint4 & a, const uint4 &
 #undef LRB_F
 }
 
-// eligibility bitmap of tile (ty, tx) for this seed; lane = row of the tile
-__device__ __forceinline__ unsigned tile_eligible(const FloodCtx & X, int ty, int tx, int lane)
+// eligibility bitmap of the 32x32 tile whose top-left pixel is (y0, x0) — x0 a multiple of 16, either may be negative
+// or beyond the frame; lane = row of the tile.  All loads are issued up front (one memory round trip per tile).
+__device__ __noinline__ unsigned tile_eligible(const FloodCtx X, int y0, int x0, int lane)
 {
-    const int y = ty * 32 + lane, x0 = tx * 32;
-    unsigned cand = 0;
-    if (y >= 1 && y < X.h - 1) {
-        const size_t ro = (size_t)y * X.pitch + x0;
-        const uint4 * pm = reinterpret_cast<const uint4 *>(X.mask8 + ro);
-        const uint4 * pv = reinterpret_cast<const uint4 *>(X.vis + ro);
-        const bool second = x0 + 16 < X.pitch;
-        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-        const uint4 m0 = __ldg(pm), v0 = __ldg(pv);
-        const uint4 m1 = second ? __ldg(pm + 1) : z, v1 = second ? __ldg(pv + 1) : z;
-        unsigned cols = 0xFFFFFFFFu;                                        // columns 1 .. w-2 only
-        if (x0 == 0) cols &= ~1u;
-        const int last = X.w - 1 - x0;                                      // first column of this tile that is NOT interior
+    // (1) mask / visited bytes of this lane's row, two 16-byte halves each
+    const int y = y0 + lane;
+    const bool rowok = y >= 1 && y < X.h - 1;
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    uint4 m0 = z, m1 = z, v0 = z, v1 = z;
+    {
+        const ptrdiff_t ro = (ptrdiff_t)y * X.pitch + x0;
+        const bool h0 = rowok && x0 >= 0 && x0 + 16 <= X.pitch, h1 = rowok && x0 + 16 >= 0 && x0 + 32 <= X.pitch;
+        if (h0) { m0 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + ro)); v0 = __ldg(reinterpret_cast<const uint4 *>(X.vis + ro)); }
+        if (h1) { m1 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + ro + 16)); v1 = __ldg(reinterpret_cast<const uint4 *>(X.vis + ro + 16)); }
+    }
+    // (2) G_b(p) > thr for every pixel of the tile, row by row with lane = column (coalesced); pixels outside the
+    //     interior read as dx = dy = 0, i.e. G = 0, which never exceeds thr >= 0
+    const int x = x0 + lane;
+    const bool colok = x >= 1 && x < X.w - 1;
+    const float * pdx = X.dx + ((ptrdiff_t)y0 * X.pitch + x);
+    const float * pdy = X.dy + ((ptrdiff_t)y0 * X.pitch + x);
+    unsigned G = 0;
+#pragma unroll
+    for (int rb = 0; rb < 32; rb += 16) {
+        float gx[16], gy[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int yy = y0 + rb + i;
+            const bool ok = colok && yy >= 1 && yy < X.h - 1;
+            const int ro = (rb + i) * X.pitch;
+            gx[i] = ok ? __ldg(pdx + ro) : 0.f;
+            gy[i] = ok ? __ldg(pdy + ro) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float g = fabsf(__fadd_rn(__fmul_rn(gx[i], X.sb), __fmul_rn(gy[i], X.cb)));
+            const unsigned bal = __ballot_sync(0xffffffffu, g > X.thr);
+            if (lane == rb + i) G = bal;
+        }
+    }
+    unsigned cols = 0xFFFFFFFFu;                                            // columns 1 .. w-2 only
+    {
+        const int first = 1 - x0;                                           // first interior column of this tile
+        if (first > 0) cols &= (first >= 32) ? 0u : ~((1u << first) - 1u);
+        const int last = X.w - 1 - x0;                                      // first column that is NOT interior
         if (last < 32) cols &= (last <= 0) ? 0u : ((1u << last) - 1u);
-        cand = bits_of_bytes(m0, m1, X.b) & ~bits_of_bytes(v0, v1, 0) & cols;
     }
-    unsigned E = 0;
-    unsigned rows = __ballot_sync(0xffffffffu, cand != 0);
-    while (rows) {                                                          // two candidate rows per trip: loads of both in flight
-        const int r0 = __ffs(rows) - 1; rows &= rows - 1;
-        const int r1 = rows ? __ffs(rows) - 1 : -1; if (rows) rows &= rows - 1;
-        const unsigned c0 = __shfl_sync(0xffffffffu, cand, r0);
-        const unsigned c1 = __shfl_sync(0xffffffffu, cand, r1 < 0 ? 0 : r1);
-        const bool p0 = (c0 >> lane) & 1u, p1 = (r1 >= 0) && ((c1 >> lane) & 1u);
-        float gx0 = 0.f, gy0 = 0.f, gx1 = 0.f, gy1 = 0.f;
-        if (p0) { const size_t po = (size_t)(ty * 32 + r0) * X.pitch + tx * 32 + lane; gx0 = __ldg(X.dx + po); gy0 = __ldg(X.dy + po); }
-        if (p1) { const size_t po = (size_t)(ty * 32 + r1) * X.pitch + tx * 32 + lane; gx1 = __ldg(X.dx + po); gy1 = __ldg(X.dy + po); }
-        const float g0 = fabsf(__fadd_rn(__fmul_rn(gx0, X.sb), __fmul_rn(gy0, X.cb)));
-        const float g1 = fabsf(__fadd_rn(__fmul_rn(gx1, X.sb), __fmul_rn(gy1, X.cb)));
-        const unsigned e0 = __ballot_sync(0xffffffffu, p0 && g0 > X.thr);
-        const unsigned e1 = __ballot_sync(0xffffffffu, p1 && g1 > X.thr);
-        if (lane == r0) E = e0;
-        if (lane == r1) E = e1;
-    }
-    return E;
+    return rowok ? (bits_of_bytes(m0, m1, X.b) & ~bits_of_bytes(v0, v1, 0) & cols & G) : 0u;
 }
 
 __device__ __forceinline__ int tab_find(const TileTab & T, int n_ent, int id, int lane)
@@ -114,24 +129,25 @@ __device__ __forceinline__ int tab_find(const TileTab & T, int n_ent, int id, in
 
 // Tentative region of one seed by one warp.  Returns the pixel count, or -1 when the table is full.
 // On success the bitmaps of the n_ent touched tiles are in T (R part).
-__device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T, int sr, int sc, int & n_ent_out)
+__device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T, int sr, int sc, int & n_ent_out, int * dbg)
 {
     const int lane = threadIdx.x & 31;
-    const int tiles_x = (X.w + 31) >> 5, tiles_y = (X.h + 31) >> 5;
+    // the tile grid is the seed's own: tile (0,0) is centred on the seed (x origin rounded to 16 for the vector loads),
+    // so that the typical small region never leaves its first tile
+    const int oy = tile_origin_y(sr), ox = tile_origin_x(sc);
     int n_ent = 1, q_head = 0, q_tail = 1;
     {   // the seed's tile; the seed itself is accepted unconditionally (filter.cpp:119-122)
-        const int ty = sr >> 5, tx = sc >> 5;
-        unsigned E = tile_eligible(X, ty, tx, lane);
-        const unsigned sbit = (lane == (sr & 31)) ? (1u << (sc & 31)) : 0u;
+        unsigned E = tile_eligible(X, oy, ox, lane);
+        const unsigned sbit = (lane == sr - oy) ? (1u << (sc - ox)) : 0u;
         E |= sbit;
         T.er[lane] = E; T.er[32 + lane] = sbit;
-        if (lane == 0) { T.ids[0] = (ty << 16) | tx; T.dirty[0] = 1; T.ring[0] = 0; }
+        if (lane == 0) { T.ids[0] = tile_id(0, 0); T.dirty[0] = 1; T.ring[0] = 0; }
         __syncwarp();
     }
     while (q_head < q_tail) {
-        const int e = T.ring[q_head % T.cap]; ++q_head;
+        const int e = T.ring[q_head % T.cap]; ++q_head; ++dbg[0];
         const int id = T.ids[e];
-        const int ty = id >> 16, tx = id & 0xFFFF;
+        const int ty = (id >> 16) - kTileBias, tx = (id & 0xFFFF) - kTileBias;
         const unsigned E = T.er[e * 64 + lane];
         unsigned R = T.er[e * 64 + 32 + lane];
         __syncwarp();
@@ -144,7 +160,7 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
             if (lane == 31) dn = 0u;
             const unsigned Rn = R | (E & (hz | up | dn));
             const bool ch = __any_sync(0xffffffffu, Rn != R);
-            R = Rn;
+            R = Rn; ++dbg[1];
             if (!ch) break;
         }
         T.er[e * 64 + 32 + lane] = R;
@@ -173,11 +189,12 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
             }
             if (!__any_sync(0xffffffffu, spill != 0u)) continue;
             const int ny = ty + dy, nx = tx + dxk;
-            if (ny < 0 || nx < 0 || ny >= tiles_y || nx >= tiles_x) continue;
-            const int nid = (ny << 16) | nx;
+            const int ny0 = oy + ny * 32, nx0 = ox + nx * 32;
+            if (ny0 + 31 < 1 || ny0 > X.h - 2 || nx0 + 31 < 1 || nx0 > X.w - 2) continue;      // no interior pixel there
+            const int nid = tile_id(ny, nx);
             int ne = tab_find(T, n_ent, nid, lane);
             if (ne < 0) {
-                const unsigned En = tile_eligible(X, ny, nx, lane);
+                const unsigned En = tile_eligible(X, ny0, nx0, lane); ++dbg[2];
                 if (!__any_sync(0xffffffffu, (En & spill) != 0u)) continue;       // nothing to reach there: do not spend an entry
                 if (n_ent >= T.cap) { n_ent_out = n_ent; return -1; }
                 ne = n_ent++;
@@ -207,14 +224,14 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
 }
 
 // stamp the region (fire-and-forget atomicMin(owner, epoch:rank)) and write its pixel list; row by row, lane = column
-__device__ __forceinline__ void emit_region(const Planes & P, unsigned * owner, const TileTab & T, int n_ent, unsigned key, unsigned * list)
+__device__ __forceinline__ void emit_region(const Planes & P, unsigned * owner, const TileTab & T, int n_ent, int oy, int ox, unsigned key, unsigned * list)
 {
     const int lane = threadIdx.x & 31;
     int off = 0;
     for (int e = 0; e < n_ent; ++e) {
         const unsigned R = T.er[e * 64 + 32 + lane];
         const int id = T.ids[e];
-        const int y0 = (id >> 16) * 32, x = (id & 0xFFFF) * 32 + lane;
+        const int y0 = oy + ((id >> 16) - kTileBias) * 32, x = ox + ((id & 0xFFFF) - kTileBias) * 32 + lane;
         unsigned rows = __ballot_sync(0xffffffffu, R != 0u);
         while (rows) {
             const int r = __ffs(rows) - 1; rows &= rows - 1;
@@ -231,11 +248,16 @@ __device__ __forceinline__ void emit_region(const Planes & P, unsigned * owner, 
 
 // one tentative flood of seed `rank` by one warp
 __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl & C, int slot, int rank,
-                                          unsigned epoch, const TileTab & Tsm)
+                                          unsigned epoch, const TileTab & Tsm, int & g_off, int & g_left)
 {
     const int lane = threadIdx.x & 31;
     const size_t so = (size_t)slot * S.cap;
-    if (__ldcg(S.status + so + rank) != kStatusLive) return;
+    const unsigned st0 = __ldcg(S.status + so + rank);
+    const unsigned spx = S.idx[so + rank];                        // independent loads: one round trip for all four
+    const int sbin = S.bin[so + rank];
+    const float sthr = S.thr[so + rank];
+    if (st0 != kStatusLive) return;
+    unsigned long long t_begin; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
 
     const size_t pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
@@ -244,51 +266,67 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
     X.w = P.w; X.h = P.h; X.pitch = P.pitch;
 
     const unsigned key = (epoch << 24) | (unsigned)rank;
-    const unsigned spx = S.idx[so + rank];
     const int sr = spx / P.w, sc = spx - sr * P.w;
     if (__ldg(X.vis + (size_t)sr * P.pitch + sc)) {               // line_detector.cpp:103: seed already swallowed
         if (lane == 0) S.status[so + rank] = kStatusDropped;
         return;
     }
-    X.b = S.bin[so + rank];
-    X.thr = S.thr[so + rank];
+    X.b = sbin;
+    X.thr = sthr;
     X.sb = kSin[X.b]; X.cb = kCos[X.b];
 
-    int n_ent = 0;
-    int size = flood_tiles(X, Tsm, sr, sc, n_ent);
+    int n_ent = 0; int dbg[3] = {0, 0, 0};
     TileTab T = Tsm;
-    int big = -1;
-    if (size < 0) {                                               // a long region: redo it on a table in global memory
-        if (lane == 0) {
-            unsigned h = (unsigned)rank * 2654435761u + blockIdx.x;
-            while (big < 0) {
-                for (int t = 0; t < K.big_slots && big < 0; ++t) {
-                    const int i = (int)((h + t) % (unsigned)K.big_slots);
-                    if (atomicCAS(K.big_lock + i, 0, 1) == 0) big = i;
+    int big = -1, size = -1;
+    for (int attempt = 0; attempt < 2 && size < 0; ++attempt) {
+        if (attempt == 1) {                                       // a long region: redo it on a table in global memory
+            if (lane == 0) {
+                unsigned h = (unsigned)rank * 2654435761u + blockIdx.x;
+                while (big < 0) {
+                    for (int t = 0; t < K.big_slots && big < 0; ++t) {
+                        const int i = (int)((h + t) % (unsigned)K.big_slots);
+                        if (atomicCAS(K.big_lock + i, 0, 1) == 0) big = i;
+                    }
+                    if (big < 0) __nanosleep(500);
                 }
-                if (big < 0) __nanosleep(500);
+                __threadfence();
             }
-            __threadfence();
+            big = __shfl_sync(0xffffffffu, big, 0);
+            char * base = reinterpret_cast<char *>(K.big) + (size_t)big * K.big_bytes;
+            T.cap = K.big_cap;
+            T.er = reinterpret_cast<unsigned *>(base);
+            T.ids = reinterpret_cast<int *>(base + (size_t)K.big_cap * 256);
+            T.dirty = T.ids + K.big_cap; T.ring = T.dirty + K.big_cap;
         }
-        big = __shfl_sync(0xffffffffu, big, 0);
-        char * base = reinterpret_cast<char *>(K.big) + (size_t)big * K.big_bytes;
-        T.cap = K.big_cap;
-        T.er = reinterpret_cast<unsigned *>(base);
-        T.ids = reinterpret_cast<int *>(base + (size_t)K.big_cap * 256);
-        T.dirty = T.ids + K.big_cap; T.ring = T.dirty + K.big_cap;
-        size = flood_tiles(X, T, sr, sc, n_ent);
+        size = flood_tiles(X, T, sr, sc, n_ent, dbg);
     }
     bool overflow = size < 0;
     int off = 0;
     if (!overflow) {
-        if (lane == 0) off = atomicAdd(&C.pool_cursor, size);
-        off = __shfl_sync(0xffffffffu, off, 0);
-        if (off + size > K.cap_pool) overflow = true;
-        else emit_region(P, owner, T, n_ent, key, K.pool + (size_t)slot * K.cap_pool + off);
+        if (size > g_left) {                                      // a new granule of list space for this warp
+            const int want = max(size, kPoolGranule);
+            if (lane == 0) g_off = atomicAdd(&C.pool_cursor, want);
+            g_off = __shfl_sync(0xffffffffu, g_off, 0);
+            g_left = (g_off + want <= K.cap_pool) ? want : -1;
+        }
+        off = g_off;
+        if (g_left < 0) { overflow = true; g_left = 0; }
+        else {
+            g_off += size; g_left -= size;
+            emit_region(P, owner, T, n_ent, tile_origin_y(sr), tile_origin_x(sc), key, K.pool + (size_t)slot * K.cap_pool + off);
+        }
     }
     __syncwarp();
     if (big >= 0 && lane == 0) { __threadfence(); atomicExch(K.big_lock + big, 0); }
     if (lane == 0) {
+#ifdef LRB_FLOOD_STATS
+        { unsigned long long t_end; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end)); const unsigned long long d = t_end - t_begin;
+          const unsigned long long pk = (d << 24) | (unsigned long long)(max(size, 0) & 0xFFFFFF);
+          if (atomicMax(&C.dbg_maxdur, pk) < pk) { C.dbg_slow[0] = dbg[0]; C.dbg_slow[1] = dbg[1]; C.dbg_slow[2] = dbg[2]; C.dbg_slow[3] = n_ent; }
+          atomicAdd(&C.dbg_sumdur, d); }
+        atomicAdd(&C.dbg_floods, 1); atomicAdd(&C.dbg_tiles, n_ent); atomicAdd(&C.dbg_px, max(size, 0)); atomicMax(&C.dbg_maxpx, size);
+        if (big >= 0) atomicAdd(&C.dbg_big, 1);
+#endif
         if (overflow) C.flood_overflow = 1;
         S.size[so + rank] = overflow ? -1 : size;
         S.list_head[so + rank] = off;
@@ -296,7 +334,7 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(FL_WARPS * 32)
+__global__ void __launch_bounds__(FL_WARPS * 32, 5)
 k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first)
 {
     __shared__ unsigned s_er[FL_WARPS][FT_SMALL * 64];
@@ -309,8 +347,9 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     const unsigned epoch = epoch_first - (unsigned)round;
     TileTab T;
     T.er = s_er[warp]; T.ids = s_ids[warp]; T.dirty = T.ids + FT_SMALL; T.ring = T.dirty + FT_SMALL; T.cap = FT_SMALL;
+    int g_off = 0, g_left = 0;
     for (int rank = lo + blockIdx.x * FL_WARPS + warp; rank < hi; rank += gridDim.x * FL_WARPS)
-        flood_one(P, S, K, C, slot, rank, epoch, T);
+        flood_one(P, S, K, C, slot, rank, epoch, T, g_off, g_left);
 }
 
 // verify + commit + mark visited, one warp per window seed; the last block to finish moves the window
@@ -359,7 +398,7 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         __threadfence();
         const int failed = atomicAdd(&C.win_live, 0);                 // window seeds that stay live (out-prioritised this round)
         const int firstf = atomicMin(&C.win_first, 0x7fffffff);
-        const int budget = max(kFloodWindowMin, n / kFloodWindowDiv);
+        const int budget = max(S.win_min, n / S.win_div);
         const int nlo = failed ? min(firstf, hi) : hi;
         const int nhi = min(n, hi + max(0, budget - failed));
         C.win_lo = nlo; C.win_hi = nhi;
