@@ -70,6 +70,8 @@ struct FrameCtrl {
     int pool_cursor;           // next free word of the pixel-list pool
     int win_live, win_first, win_blocks;   // commit-kernel scratch (live seeds left in the window, lowest of them, blocks done)
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
+    int queue[kMaxRounds + 1]; // queue[r]: next window position handed out in flood round r (warps take seeds dynamically, in priority order)
+    int fit_queue;             // next kept component handed out by the fit kernel
     // grouping state
     int num_obs;               // reference estimator.h:119
     int n_solves;

@@ -319,8 +319,8 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     launch_seed_order(e->P, e->S, e->ctrl, n, e->S.cap, e->st);
     stage(LRB_T_FLOOD);
     int rounds = kInitialRounds;
-    launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
-    e->kernels += 2 + 1 + 3 + 2 * rounds;
+    e->kernels += launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
+    e->kernels += 2 + 1 + 3;
     if (debug_sync) {
         stage(LRB_T_FIT); launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds, e->st);
         stage(LRB_T_MODEL); launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds, e->st);
@@ -361,8 +361,8 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         if (!more_rounds && !serial && !more_stream) break;
         if (more_rounds && !serial) {
             if (rounds + 16 <= kMaxRounds) {
-                launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
-                e->kernels += 32; rounds += 16;
+                e->kernels += launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
+                rounds += 16;
             } else serial = true;
         }
         if (serial) {

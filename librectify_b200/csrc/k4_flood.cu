@@ -21,6 +21,7 @@
 // mask8, dx, dy and the visited mask — through the non-coherent path; the owner stamps are write-only here and are
 // inspected by the verify kernel.  owner word = [epoch | rank]; epochs DEcrease from round to round and frame to frame,
 // so a newer stamp always wins over stale ones and the plane is re-initialised only when the epoch field wraps.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -69,42 +70,49 @@ __device__ __forceinline__ unsigned bits_of_bytes(const uint4 & a, const uint4 &
 
 // eligibility bitmap of the 32x32 tile whose top-left pixel is (y0, x0) — x0 a multiple of 16, either may be negative
 // or beyond the frame; lane = row of the tile.  All loads are issued up front (one memory round trip per tile).
-__device__ __noinline__ unsigned tile_eligible(const FloodCtx X, int y0, int x0, int lane)
+// Branch-free on purpose: every address is clamped into the plane and what lies outside the interior is masked out
+// afterwards, so the function is ~5 KB of straight-line code (the predicated form was 29 KB — with 20+ warps per SM at
+// different places of a 70 KB kernel the instruction cache was the bottleneck: ncu "no instruction" stalls).
+// Returns (visited bitmap << 32) | eligible bitmap.  RB = rows whose dx/dy loads are in flight together (16: two dependent
+// batches, 64 live registers less; 32: a single batch).
+template <int RB>
+__device__ __noinline__ unsigned long long tile_eligible(const FloodCtx X, int y0, int x0, int lane)
 {
     // (1) mask / visited bytes of this lane's row, two 16-byte halves each
     const int y = y0 + lane;
     const bool rowok = y >= 1 && y < X.h - 1;
-    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    uint4 m0 = z, m1 = z, v0 = z, v1 = z;
-    {
-        const ptrdiff_t ro = (ptrdiff_t)y * X.pitch + x0;
-        const bool h0 = rowok && x0 >= 0 && x0 + 16 <= X.pitch, h1 = rowok && x0 + 16 >= 0 && x0 + 32 <= X.pitch;
-        if (h0) { m0 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + ro)); v0 = __ldg(reinterpret_cast<const uint4 *>(X.vis + ro)); }
-        if (h1) { m1 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + ro + 16)); v1 = __ldg(reinterpret_cast<const uint4 *>(X.vis + ro + 16)); }
-    }
-    // (2) G_b(p) > thr for every pixel of the tile, row by row with lane = column (coalesced); pixels outside the
-    //     interior read as dx = dy = 0, i.e. G = 0, which never exceeds thr >= 0
-    const int x = x0 + lane;
-    const bool colok = x >= 1 && x < X.w - 1;
-    const float * pdx = X.dx + ((ptrdiff_t)y0 * X.pitch + x);
-    const float * pdy = X.dy + ((ptrdiff_t)y0 * X.pitch + x);
+    const bool h0 = x0 >= 0 && x0 + 16 <= X.pitch, h1 = x0 + 16 >= 0 && x0 + 32 <= X.pitch;      // warp-uniform
+    const ptrdiff_t rbase = (ptrdiff_t)min(max(y, 0), X.h - 1) * X.pitch;
+    const ptrdiff_t o0 = rbase + (h0 ? x0 : 0), o1 = rbase + (h1 ? x0 + 16 : 0);
+    const uint4 m0 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + o0)), v0 = __ldg(reinterpret_cast<const uint4 *>(X.vis + o0));
+    const uint4 m1 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + o1)), v1 = __ldg(reinterpret_cast<const uint4 *>(X.vis + o1));
+    // (2) G_b(p) > thr for every pixel of the tile, row by row with lane = column (coalesced).  Rows outside the
+    //     interior are dropped by `rowok` of the lane that keeps them, columns outside it by the `cols` mask below.
     unsigned G = 0;
+    if (y0 >= 0 && y0 + 32 <= X.h && x0 >= 0 && x0 + 32 <= X.pitch) {       // the tile lies inside the plane (warp-uniform): no clamping
+        const float * pdx = X.dx + ((ptrdiff_t)y0 * X.pitch + x0 + lane);
+        const float * pdy = X.dy + ((ptrdiff_t)y0 * X.pitch + x0 + lane);
+        const int pitch = X.pitch;
 #pragma unroll
-    for (int rb = 0; rb < 32; rb += 16) {
-        float gx[16], gy[16];
+        for (int rb = 0; rb < 32; rb += RB) {
+            float gx[RB], gy[RB];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int yy = y0 + rb + i;
-            const bool ok = colok && yy >= 1 && yy < X.h - 1;
-            const int ro = (rb + i) * X.pitch;
-            gx[i] = ok ? __ldg(pdx + ro) : 0.f;
-            gy[i] = ok ? __ldg(pdy + ro) : 0.f;
+            for (int i = 0; i < RB; ++i) { gx[i] = __ldg(pdx + (rb + i) * pitch); gy[i] = __ldg(pdy + (rb + i) * pitch); }
+#pragma unroll
+            for (int i = 0; i < RB; ++i) {
+                const float g = fabsf(__fadd_rn(__fmul_rn(gx[i], X.sb), __fmul_rn(gy[i], X.cb)));
+                const unsigned bal = __ballot_sync(0xffffffffu, g > X.thr);
+                G = (lane == rb + i) ? bal : G;
+            }
         }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const float g = fabsf(__fadd_rn(__fmul_rn(gx[i], X.sb), __fmul_rn(gy[i], X.cb)));
+    } else {                                                                // frame border: clamped addresses, rolled loop
+        const int xc = min(max(x0 + lane, 0), X.pitch - 1);
+#pragma unroll 1
+        for (int i = 0; i < 32; ++i) {
+            const ptrdiff_t ro = (ptrdiff_t)min(max(y0 + i, 0), X.h - 1) * X.pitch + xc;
+            const float g = fabsf(__fadd_rn(__fmul_rn(__ldg(X.dx + ro), X.sb), __fmul_rn(__ldg(X.dy + ro), X.cb)));
             const unsigned bal = __ballot_sync(0xffffffffu, g > X.thr);
-            if (lane == rb + i) G = bal;
+            G = (lane == i) ? bal : G;
         }
     }
     unsigned cols = 0xFFFFFFFFu;                                            // columns 1 .. w-2 only
@@ -114,7 +122,10 @@ __device__ __noinline__ unsigned tile_eligible(const FloodCtx X, int y0, int x0,
         const int last = X.w - 1 - x0;                                      // first column that is NOT interior
         if (last < 32) cols &= (last <= 0) ? 0u : ((1u << last) - 1u);
     }
-    return rowok ? (bits_of_bytes(m0, m1, X.b) & ~bits_of_bytes(v0, v1, 0) & cols & G) : 0u;
+    const unsigned lo = h0 ? 0x0000FFFFu : 0u, hi = h1 ? 0xFFFF0000u : 0u;  // halves that lie outside the pitch
+    const unsigned V = bits_of_bytes(v0, v1, 0);
+    const unsigned E = rowok ? (bits_of_bytes(m0, m1, X.b) & ~V & cols & G & (lo | hi)) : 0u;
+    return ((unsigned long long)V << 32) | E;
 }
 
 __device__ __forceinline__ int tab_find(const TileTab & T, int n_ent, int id, int lane)
@@ -127,8 +138,11 @@ __device__ __forceinline__ int tab_find(const TileTab & T, int n_ent, int id, in
     return -1;
 }
 
-// Tentative region of one seed by one warp.  Returns the pixel count, or -1 when the table is full.
+// Tentative region of one seed by one warp.  Returns the pixel count, -1 when the table is full, or -2 when the seed
+// pixel is already visited (line_detector.cpp:103: the seed was swallowed by an earlier region; its visited byte comes
+// with the seed tile, so no separate memory round trip is spent on it).
 // On success the bitmaps of the n_ent touched tiles are in T (R part).
+template <int RB>
 __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T, int sr, int sc, int & n_ent_out, int * dbg)
 {
     const int lane = threadIdx.x & 31;
@@ -137,8 +151,10 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
     const int oy = tile_origin_y(sr), ox = tile_origin_x(sc);
     int n_ent = 1, q_head = 0, q_tail = 1;
     {   // the seed's tile; the seed itself is accepted unconditionally (filter.cpp:119-122)
-        unsigned E = tile_eligible(X, oy, ox, lane);
+        const unsigned long long ve = tile_eligible<RB>(X, oy, ox, lane);
+        unsigned E = (unsigned)ve;
         const unsigned sbit = (lane == sr - oy) ? (1u << (sc - ox)) : 0u;
+        if (__any_sync(0xffffffffu, ((unsigned)(ve >> 32) & sbit) != 0u)) { n_ent_out = 0; return -2; }
         E |= sbit;
         T.er[lane] = E; T.er[32 + lane] = sbit;
         if (lane == 0) { T.ids[0] = tile_id(0, 0); T.dirty[0] = 1; T.ring[0] = 0; }
@@ -169,8 +185,8 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
         const bool edge = __any_sync(0xffffffffu, (R & 0x80000001u) != 0u || ((lane == 0 || lane == 31) && R != 0u));
         if (!edge) continue;
         const unsigned hr = R >> 31, hl = (R & 1u) << 31;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
+#pragma unroll 1
+        for (int k = 0; k < 8; ++k) {                                       // rolled: the kernel has to stay inside the instruction cache
             const int dy = (k < 3) ? -1 : (k < 5 ? 0 : 1);
             const int dxk = (k < 3) ? k - 1 : (k < 5 ? (k == 3 ? -1 : 1) : k - 6);
             const unsigned src = dxk == 0 ? hz : (dxk > 0 ? hr : hl);
@@ -194,7 +210,7 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
             const int nid = tile_id(ny, nx);
             int ne = tab_find(T, n_ent, nid, lane);
             if (ne < 0) {
-                const unsigned En = tile_eligible(X, ny0, nx0, lane); ++dbg[2];
+                const unsigned En = (unsigned)tile_eligible<RB>(X, ny0, nx0, lane); ++dbg[2];
                 if (!__any_sync(0xffffffffu, (En & spill) != 0u)) continue;       // nothing to reach there: do not spend an entry
                 if (n_ent >= T.cap) { n_ent_out = n_ent; return -1; }
                 ne = n_ent++;
@@ -223,7 +239,10 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
     return cnt;
 }
 
-// stamp the region (fire-and-forget atomicMin(owner, epoch:rank)) and write its pixel list; row by row, lane = column
+// stamp the region (fire-and-forget atomicMin(owner, epoch:rank)) and write its pixel list (any order: the verify kernel
+// only needs the set, the fit re-walks the region in the reference's order).  Per tile either lane = row, every lane
+// walking the set bits of its own row, or row by row with lane = column — whichever takes fewer iterations (a vertical
+// line has 32 rows of 1-3 pixels, a horizontal one 1-3 rows of 32).
 __device__ __forceinline__ void emit_region(const Planes & P, unsigned * owner, const TileTab & T, int n_ent, int oy, int ox, unsigned key, unsigned * list)
 {
     const int lane = threadIdx.x & 31;
@@ -231,22 +250,44 @@ __device__ __forceinline__ void emit_region(const Planes & P, unsigned * owner, 
     for (int e = 0; e < n_ent; ++e) {
         const unsigned R = T.er[e * 64 + 32 + lane];
         const int id = T.ids[e];
-        const int y0 = oy + ((id >> 16) - kTileBias) * 32, x = ox + ((id & 0xFFFF) - kTileBias) * 32 + lane;
+        const int y0 = oy + ((id >> 16) - kTileBias) * 32, x0 = ox + ((id & 0xFFFF) - kTileBias) * 32;
+        const int c = __popc(R);
         unsigned rows = __ballot_sync(0xffffffffu, R != 0u);
-        while (rows) {
-            const int r = __ffs(rows) - 1; rows &= rows - 1;
-            const unsigned m = __shfl_sync(0xffffffffu, R, r);
-            if ((m >> lane) & 1u) {
-                const int y = y0 + r;
-                atomicMin(owner + (size_t)y * P.pitch + x, key);
-                list[off + __popc(m & ((1u << lane) - 1u))] = ((unsigned)y << 16) | (unsigned)x;
+        if (rows == 0u) continue;
+        const int maxc = __reduce_max_sync(0xffffffffu, c);
+        if (maxc <= __popc(rows)) {                                         // lane = row
+            int pre = c;
+#pragma unroll
+            for (int sft = 1; sft < 32; sft <<= 1) { const int v = __shfl_up_sync(0xffffffffu, pre, sft); if (lane >= sft) pre += v; }
+            const int total = __shfl_sync(0xffffffffu, pre, 31);
+            int i = off + pre - c;
+            const int y = y0 + lane;
+            unsigned * orow = owner + (size_t)y * P.pitch + x0;
+            unsigned m = R;
+            while (m) {
+                const int bcol = __ffs(m) - 1; m &= m - 1;
+                atomicMin(orow + bcol, key);
+                list[i++] = ((unsigned)y << 16) | (unsigned)(x0 + bcol);
             }
-            off += __popc(m);
+            off += total;
+        } else {                                                            // row by row, lane = column
+            const int x = x0 + lane;
+            while (rows) {
+                const int r = __ffs(rows) - 1; rows &= rows - 1;
+                const unsigned m = __shfl_sync(0xffffffffu, R, r);
+                if ((m >> lane) & 1u) {
+                    const int y = y0 + r;
+                    atomicMin(owner + (size_t)y * P.pitch + x, key);
+                    list[off + __popc(m & ((1u << lane) - 1u))] = ((unsigned)y << 16) | (unsigned)x;
+                }
+                off += __popc(m);
+            }
         }
     }
 }
 
 // one tentative flood of seed `rank` by one warp
+template <int RB>
 __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl & C, int slot, int rank,
                                           unsigned epoch, const TileTab & Tsm, int & g_off, int & g_left)
 {
@@ -267,10 +308,6 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
 
     const unsigned key = (epoch << 24) | (unsigned)rank;
     const int sr = spx / P.w, sc = spx - sr * P.w;
-    if (__ldg(X.vis + (size_t)sr * P.pitch + sc)) {               // line_detector.cpp:103: seed already swallowed
-        if (lane == 0) S.status[so + rank] = kStatusDropped;
-        return;
-    }
     X.b = sbin;
     X.thr = sthr;
     X.sb = kSin[X.b]; X.cb = kCos[X.b];
@@ -278,7 +315,7 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
     int n_ent = 0; int dbg[3] = {0, 0, 0};
     TileTab T = Tsm;
     int big = -1, size = -1;
-    for (int attempt = 0; attempt < 2 && size < 0; ++attempt) {
+    for (int attempt = 0; attempt < 2 && size == -1; ++attempt) {
         if (attempt == 1) {                                       // a long region: redo it on a table in global memory
             if (lane == 0) {
                 unsigned h = (unsigned)rank * 2654435761u + blockIdx.x;
@@ -298,7 +335,11 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
             T.ids = reinterpret_cast<int *>(base + (size_t)K.big_cap * 256);
             T.dirty = T.ids + K.big_cap; T.ring = T.dirty + K.big_cap;
         }
-        size = flood_tiles(X, T, sr, sc, n_ent, dbg);
+        size = flood_tiles<RB>(X, T, sr, sc, n_ent, dbg);
+    }
+    if (size == -2) {                                             // line_detector.cpp:103: seed already swallowed
+        if (lane == 0) S.status[so + rank] = kStatusDropped;
+        return;
     }
     bool overflow = size < 0;
     int off = 0;
@@ -334,12 +375,13 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(FL_WARPS * 32, 5)
-k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first)
+template <int MINB, int RB>
+__global__ void __launch_bounds__(FL_WARPS * 32, MINB)
+k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first, int slot0)
 {
     __shared__ unsigned s_er[FL_WARPS][FT_SMALL * 64];
     __shared__ int s_ids[FL_WARPS][FT_SMALL * 3];
-    const int slot = blockIdx.y;
+    const int slot = slot0 + blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
     const int lo = C.win_lo, hi = C.win_hi;
@@ -348,16 +390,27 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     TileTab T;
     T.er = s_er[warp]; T.ids = s_ids[warp]; T.dirty = T.ids + FT_SMALL; T.ring = T.dirty + FT_SMALL; T.cap = FT_SMALL;
     int g_off = 0, g_left = 0;
-    for (int rank = lo + blockIdx.x * FL_WARPS + warp; rank < hi; rank += gridDim.x * FL_WARPS)
-        flood_one(P, S, K, C, slot, rank, epoch, T, g_off, g_left);
+    // Seeds are handed out dynamically, one at a time and in priority order (the strongest seeds own the longest regions,
+    // so the long floods start first and the short ones fill the gaps); the next position is requested before the
+    // current flood starts so that the round trip of the atomic is hidden behind it.
+    const int lane = threadIdx.x & 31;
+    int * q = &C.queue[round];
+    int nxt = 0;
+    if (lane == 0) nxt = atomicAdd(q, 1);
+    while (true) {
+        const int rank = lo + __shfl_sync(0xffffffffu, nxt, 0);
+        if (rank >= hi) break;
+        if (lane == 0) nxt = atomicAdd(q, 1);
+        flood_one<RB>(P, S, K, C, slot, rank, epoch, T, g_off, g_left);
+    }
 }
 
 // verify + commit + mark visited, one warp per window seed; the last block to finish moves the window
 __global__ void __launch_bounds__(256)
-k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first)
+k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first, int slot0)
 {
     __shared__ int s_last;
-    const int slot = blockIdx.y;
+    const int slot = slot0 + blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
     const int n = C.n_seeds;
@@ -483,16 +536,36 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_seri
 
 } // namespace
 
-void launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int seeds_hint,
+int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int seeds_hint,
                          int round_begin, int round_end, unsigned epoch_first, cudaStream_t st)
 {
-    // flood: CTAs striding over the window's ranks; verify: warps striding over the window
-    const int fblocks = max(1, min((seeds_hint + FL_WARPS - 1) / FL_WARPS, 148 * 8 / max(1, min(n_slots, 4))));
-    dim3 gf(fblocks, n_slots), gv(148 / max(1, min(n_slots, 4)) + 1, n_slots);
-    for (int r = round_begin; r < round_end; ++r) {
-        k_flood_round<<<gf, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first);
-        k_flood_verify<<<gv, 256, 0, st>>>(P, S, K, ctrl, r, epoch_first);
+    // flood: a resident set of CTAs per frame, warps pull seeds from the frame's queue; verify: warps striding over the window
+    // register budget of the flood kernel: MINB resident CTAs per SM (LRB_FLOOD_MINB=4|5|6|8 for experiments; 4 loads a tile's 32 rows in one batch)
+    static const int minb = [] { const char * v = getenv("LRB_FLOOD_MINB"); return v ? atoi(v) : 4; }();
+    auto kern = (minb >= 8) ? k_flood_round<8, 16> : (minb == 6) ? k_flood_round<6, 16> : (minb == 4) ? k_flood_round<4, 32> : k_flood_round<5, 16>;
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FL_WARPS * 32, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
     }
+    int n_sm = 148; { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
+    // LRB_FLOOD_SUB=k floods k frames at a time (all rounds of one sub-batch, then the next) to keep their planes L2
+    // resident.  Measured on B200 (gpurun_out/sweep4.log): slower at every k < n_slots — a round is bound by its longest
+    // flood chain, not by bandwidth, so more frames in flight win — hence the default is one batch of all slots.
+    static const int sub_env = [] { const char * v = getenv("LRB_FLOOD_SUB"); return v ? atoi(v) : 0; }();
+    int sub = sub_env > 0 ? sub_env : n_slots;
+    sub = max(1, min(sub, n_slots));
+    int launches = 0;
+    for (int s0 = 0; s0 < n_slots; s0 += sub) {
+        const int ns = min(sub, n_slots - s0);
+        const int fblocks = max(1, min((seeds_hint + FL_WARPS - 1) / FL_WARPS, (n_sm * per_sm + ns - 1) / ns));
+        dim3 gf(fblocks, ns), gv(148 / max(1, min(ns, 4)) + 1, ns);
+        for (int r = round_begin; r < round_end; ++r) {
+            kern<<<gf, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
+            k_flood_verify<<<gv, 256, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
+            launches += 2;
+        }
+    }
+    return launches;                                                        // kernels launched (the engine counts them)
 }
 
 void launch_flood_serial(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots,

@@ -20,6 +20,7 @@ namespace lrb {
 namespace {
 
 constexpr int FIT_WARPS = 4;
+constexpr int FIT_RING = 256;        // power of two
 
 static __device__ __constant__ const int kDr[8] = {0, 0, 1, -1, -1, -1, 1, 1};
 static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
@@ -37,7 +38,7 @@ __global__ void __launch_bounds__(1024) k_comp_select(Seeds S, Comps K, FrameCtr
     if (C.fit_done) return;                               // repair pass for another slot: this one is already fitted
     // floods not finished (more rounds or the serial fallback needed): publish nothing; the host re-runs from here
     if ((C.live[rounds_total] != 0 && !C.flood_done) || C.flood_overflow) {
-        if (t == 0) { C.n_comp = 0; C.n_px = 0; }
+        if (t == 0) { C.n_comp = 0; C.n_px = 0; C.fit_queue = 0; }
         return;
     }
     if (t == 0) { base_c = 0; base_px = 0; }
@@ -79,7 +80,7 @@ __global__ void __launch_bounds__(1024) k_comp_select(Seeds S, Comps K, FrameCtr
         if (t == 0) { base_c += wcnt[31]; base_px += wpx[31]; }
         __syncthreads();
     }
-    if (t == 0) { C.n_comp = min(base_c, K.cap); C.n_px = base_px; }
+    if (t == 0) { C.n_comp = min(base_c, K.cap); C.n_px = base_px; C.fit_queue = 0; }
 }
 
 // running sums evaluated strictly in list order: lanes 0..NS-1 each own one sum; terms come through shared memory
@@ -102,17 +103,26 @@ __global__ void __launch_bounds__(FIT_WARPS * 32)
 k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
 {
     __shared__ float stage_all[FIT_WARPS][3][32];
+    __shared__ unsigned ring_all[FIT_WARPS][FIT_RING];     // the last FIT_RING accepted pixels of the walk (the BFS frontier lives here)
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.fit_done) return;
     const int ncomp = C.n_comp;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float (*stage)[32] = stage_all[warp];
+    unsigned * ring = ring_all[warp];
     const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap, pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
     const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
 
-    for (int comp = blockIdx.x * FIT_WARPS + warp; comp < ncomp; comp += gridDim.x * FIT_WARPS) {
+    // components are handed out dynamically in seed order (large components tend to come first); the next one is
+    // requested before the current one is walked
+    int nxt = 0;
+    if (lane == 0) nxt = atomicAdd(&C.fit_queue, 1);
+    while (true) {
+        const int comp = __shfl_sync(0xffffffffu, nxt, 0);
+        if (comp >= ncomp) break;
+        if (lane == 0) nxt = atomicAdd(&C.fit_queue, 1);
         const int rank = K.rank[ko + comp];
         const int n = K.size[ko + comp];
         unsigned * px = K.px + (size_t)slot * K.cap_px + K.off[ko + comp];
@@ -123,10 +133,13 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
         const unsigned spx = S.idx[so + rank];
 
         // ---- pixel list in the reference's acceptance order (filter.cpp:123-151) ----------------------------------
+        // The frontier is read from a shared-memory ring (one memory round trip per step: the owner probe); the list in
+        // global memory is write-only here unless the frontier outgrows the ring.
         int head = 0, tail = 1;
         if (lane == 0) {
             const int sr = spx / P.w, sc = spx - sr * P.w;
-            __stcg(px, ((unsigned)sr << 16) | (unsigned)sc);
+            const unsigned rc0 = ((unsigned)sr << 16) | (unsigned)sc;
+            __stcg(px, rc0); ring[0] = rc0;
             __stcg(owner + (size_t)sr * P.pitch + sc, listed);
         }
         __syncwarp();
@@ -134,7 +147,8 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             const int cnt = min(4, tail - head);
             const int pslot = lane >> 3, k = lane & 7;
             const bool act = pslot < cnt;
-            const unsigned prc = __ldcg(px + head + (act ? pslot : 0));
+            const int pi = head + (act ? pslot : 0);
+            const unsigned prc = (tail - pi <= FIT_RING) ? ring[pi & (FIT_RING - 1)] : __ldcg(px + pi);
             head += cnt;
             const int r = (int)(prc >> 16) + kDr[k], c = (int)(prc & 0xFFFFu) + kDc[k];
             const size_t po = (size_t)r * P.pitch + c;                          // parents are interior pixels: in range
@@ -144,9 +158,11 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             const unsigned same = __match_any_sync(0xffffffffu, mkey);
             const bool take = member && (lane == __ffs(same) - 1);
             const unsigned tm = __ballot_sync(0xffffffffu, take);
+            __syncwarp();                                                       // every lane has read its parent: ring entries may be overwritten
             if (take) {
                 const int pos = tail + __popc(tm & ((1u << lane) - 1));
                 if (pos < n) __stcg(px + pos, rcq);
+                ring[pos & (FIT_RING - 1)] = rcq;
                 __stcg(owner + po, listed);
             }
             tail += __popc(tm);

@@ -17,7 +17,7 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st);
 void nms_tile_dims(int * mw, int * mh, int * bw, int * bh);
 // k4_flood.cu
-void launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int seeds_hint,
+int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int seeds_hint,
                          int round_begin, int round_end, unsigned epoch_first, cudaStream_t st);
 void launch_flood_serial(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots,
                          unsigned epoch_serial, cudaStream_t st);
