@@ -31,6 +31,7 @@ W, H = 1920, 1080
 MIN_LENGTH = 19.2
 METRIC = "1080p images/sec (detect+VP+transform)"
 K1_BYTES_PER_PX = 17.0          # 4 B read (image) + 8 B (dx, dy) + 4 B (mag) + 1 B (bin) written
+K1_NCU_DRAM_BYTES_PER_PX = (66.382592e6 + 156.580608e6) / (8 * 1920 * 1080)   # measured DRAM traffic of K1 (ncu, 8 frames per launch): 13.4 B/px — stores still in L2 at kernel end are not counted
 K2_BYTES_PER_PX = 6.0           # 4 B (mag) + 1 B (bin) read, 1 B (mask8) written
 
 
@@ -133,7 +134,7 @@ def run_reference(args):
 
 
 # ---- this repo's arm ----------------------------------------------------------------------------------------------------
-def cpu_baseline_sample(n_frames=6):
+def cpu_baseline_sample(n_frames=48):
     """the reference's OpenMP CPU path on the box's host cores, on a bounded sample of the same workload (rank 0, N=1)"""
     try:
         from oracle.bind import Ref, RectificationConfig, ref_available, Oracle
@@ -262,7 +263,8 @@ def run_b200(args):
         "latency_ms_p50_single_frame": lat_p50,
         "gpu_launches": int(prof["kernels"]),
         "roofline": {"kernel": "k_grad5x5_bin (K1)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak if peak else None, "traffic": K1_NCU_DRAM_BYTES_PER_PX * W * H * frames_per_launch,
+                     "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one 8-frame launch (profiles/r1_k1_full.md), scaled to this launch size", "peak_source": peak_src,
                      "algorithmic_bytes_per_px": K1_BYTES_PER_PX, "frames_per_launch": frames_per_launch, "ms_per_launch": k1_ms,
                      "k2_nms_GBps": (K2_BYTES_PER_PX * W * H * frames_per_launch / (k2_ms * 1e-3) / 1e9) if k2_ms > 0 else None},
         "stage_ms_per_frame": stage_ms_per_frame,
@@ -284,12 +286,12 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames", type=int, default=64, help="frames per GPU per step")
+    ap.add_argument("--frames", type=int, default=128, help="frames per GPU per step")
     ap.add_argument("--engines", type=int, default=4, help="engines (streams + workspaces) per GPU")
-    ap.add_argument("--slots", type=int, default=8, help="frame slots per engine (frames per launch group)")
+    ap.add_argument("--slots", type=int, default=32, help="frame slots per engine (frames per launch group)")
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm (bounded CPU sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
