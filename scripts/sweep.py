@@ -33,6 +33,6 @@ for e, s, f in shapes:
     for _ in range(3):
         r.rectify(host[:f].numpy(), ML, cfg)
     torch.cuda.synchronize(); dth = time.perf_counter() - t0
-    st = {k: round(v / (3 * f), 3) for k, v in p["ms"].items()}
+    st = {k: round(v / (3 * f), 4) for k, v in p["ms"].items()}
     print(e, s, f, round(3 * f / dt), round(3 * f / dth), st, "fallbacks", int(info["flood_fallback"].sum()), flush=True)
     r.close()
