@@ -58,7 +58,7 @@ using InputPixelType = float;
 /* Detect segments and group them into at most four pencils (reference src/librectify.h:111-116,
  * src/interface.cpp:35-80).
  *   min_length  segments not longer than max(min_length, 5) px, or with err >= 2, are dropped
- *   refine      accepted for ABI compatibility; the merge post-process is a later scope row and is ignored
+ *   refine      merge collinear, overlapping raw segments before the filter (src/line_detector.cpp:340-444), as the reference does
  *   num_threads accepted and ignored (the reference's OpenMP thread count; the GPU path has no use for it)
  *   n_lines     receives the element count of the returned array
  * Returns an array owned by the caller (free it with release_line_segments), or nullptr with *n_lines = 0

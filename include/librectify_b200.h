@@ -58,6 +58,10 @@ LRB_API const char * lrb_version(void);
 /* Seed of the sampler's mt19937 for engines created afterwards and for the drop-in API (the reference seeds from
  * std::random_device, reference src/estimator.h:35; a fixed seed — default 0 — makes the library deterministic). */
 LRB_API void lrb_set_seed(unsigned seed);
+/* `refine` of find_line_segment_groups (reference src/librectify.h:111-116, src/interface.cpp:56-59, src/line_detector.cpp:340-444):
+ * merge collinear, overlapping raw segments before the length/err filter.  Off by default; applies to the following lrb_detect_* /
+ * lrb_rectify_* calls on this engine.  The drop-in find_line_segment_groups sets it from its own `refine` argument. */
+LRB_API int lrb_engine_set_refine(lrb_engine * e, int on);
 
 /* One engine = one device + one stream + workspace for `slots` frames processed per launch group. */
 LRB_API int  lrb_engine_create(int device, int slots, lrb_engine ** out);
@@ -109,7 +113,8 @@ enum lrb_stage {
     LRB_ST_PAIRS,                                /* int32   [10000*2]: samples of the LAST solve */
     LRB_ST_SCORES,                               /* float32 [4*10000] (-1 = rejected sample) */
     LRB_ST_RANSAC,                               /* int32 winner[4], float best_h[12], float refined[12] = 28 words */
-    LRB_ST_STREAM                                /* uint32 [count]: head of the uniform stream (k = 2^32 u) */
+    LRB_ST_STREAM,                               /* uint32 [count]: head of the uniform stream (k = 2^32 u) */
+    LRB_ST_REFINED_SEGS                          /* lrb_segment [n_merged]: raw segments after the `refine` merge (engine refine on) */
 };
 LRB_API long long lrb_stage_fetch(lrb_engine * e, int slot, int stage, void * dst, size_t dst_bytes);
 

@@ -34,7 +34,7 @@ INFO_DTYPE = np.dtype([("n_lines", "<i4"), ("n_seeds", "<i4"), ("n_components", 
 assert SEG_DTYPE.itemsize == 28 and TF_DTYPE.itemsize == 80 and CFG_DTYPE.itemsize == 20 and INFO_DTYPE.itemsize == 48
 
 STAGES = dict(dx=0, dy=1, mag=2, bin=3, mask8=4, seeds=5, labels=6, comp_sizes=7, raw_segs=8, model_h=9, model_anchor=10,
-              model_dir=11, model_len=12, model_bbox=13, pairs=14, scores=15, ransac=16, stream=17)
+              model_dir=11, model_len=12, model_bbox=13, pairs=14, scores=15, ransac=16, stream=17, refined_segs=18)
 TIMERS = ("ingest", "grad", "nms", "seeds", "flood", "fit", "model", "ransac", "readback")
 
 
@@ -58,6 +58,7 @@ def load_library(path: str | None = None):
     lib.lrb_last_error.restype = C.c_char_p
     lib.lrb_version.restype = C.c_char_p
     lib.lrb_set_seed.argtypes = [C.c_uint]; lib.lrb_set_seed.restype = None
+    lib.lrb_engine_set_refine.argtypes = [vp, ip]
     lib.lrb_engine_create.argtypes = [ip, ip, C.POINTER(vp)]
     lib.lrb_engine_destroy.argtypes = [vp]; lib.lrb_engine_destroy.restype = None
     lib.lrb_engine_slots.argtypes = [vp]
@@ -200,6 +201,10 @@ class Engine:
         if rc != 0:
             raise LibrectifyError(_err(self.lib))
 
+    def set_refine(self, on: bool = True):
+        """the reference's ``refine`` flag (src/interface.cpp:56-59) for the following detect / rectify calls"""
+        self._check(self.lib.lrb_engine_set_refine(self.h, 1 if on else 0))
+
     @staticmethod
     def _frames_args(frames):
         """(pointer, n, h, w, pitch, frame_stride, on_device, keepalive) for a numpy array or a torch tensor [n,h,w] / [h,w]."""
@@ -250,7 +255,7 @@ class Engine:
             buf = np.zeros(count or 16, np.uint32)
         else:
             cap = count if count is not None else (w * h // 4 + 4096)
-            dt = {"seeds": np.int32, "comp_sizes": np.int32, "raw_segs": SEG_DTYPE}.get(stage, np.float32)
+            dt = {"seeds": np.int32, "comp_sizes": np.int32, "raw_segs": SEG_DTYPE, "refined_segs": SEG_DTYPE}.get(stage, np.float32)
             mult = {"seeds": 2, "model_h": 3, "model_anchor": 2, "model_dir": 2}.get(stage, 1)
             buf = np.zeros(cap * mult, dt)
         got = self.lib.lrb_stage_fetch(self.h, slot, STAGES[stage], buf.ctypes.data, buf.nbytes)

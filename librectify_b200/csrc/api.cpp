@@ -47,13 +47,14 @@ namespace librectify {
 extern "C" {
 
 LineSegment * find_line_segment_groups(InputPixelType * buffer, int width, int height, int stride, float min_length,
-                                       bool /*refine: later scope row*/, int /*num_threads: OpenMP only*/, int * n_lines)
+                                       bool refine, int /*num_threads: OpenMP only*/, int * n_lines)
 {
     *n_lines = 0;
     int device = 0;
     if (cudaGetDevice(&device) != cudaSuccess) return nullptr;
     lrb_engine * e = pool().take(device);
     if (!e) return nullptr;
+    lrb_engine_set_refine(e, refine ? 1 : 0);                         // interface.cpp:56-59
     lrb_frame_info info;
     LineSegment * res = nullptr;
     // first pass copies at most 4096 segments; a frame with more is fetched again with the exact size

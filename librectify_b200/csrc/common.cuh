@@ -72,6 +72,7 @@ struct FrameCtrl {
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
     int queue[kMaxRounds + 1]; // queue[r]: next window position handed out in flood round r (warps take seeds dynamically, in priority order)
     int fit_queue;             // next kept component handed out by the fit kernel
+    int n_edges, n_merged, refine_overflow;   // `refine` post-process (k_refine.cu): collinearity edges, merged segments, edge list full
     // grouping state
     int num_obs;               // reference estimator.h:119
     int n_solves;

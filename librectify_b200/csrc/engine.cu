@@ -98,6 +98,7 @@ struct lrb_engine {
     int * labels = nullptr;            // debug plane (lazily used)
     CUtensorMap tm_img{}, tm_mag{}, tm_bin{};
     unsigned next_epoch = 0xFE;
+    bool refine = false;               // run the `refine` merge post-process (reference interface.cpp:56-59)
     int seed_div = 8;                  // seed capacity = pixels / seed_div; grown to 1 the first time a frame needs it
     // uniform stream
     unsigned * stream = nullptr; unsigned long long stream_len = 0; unsigned seed = 0;
@@ -224,7 +225,8 @@ void enqueue_tail(lrb_engine * e, int n, float min_length, int rounds_total, Tic
     tk.at(LRB_T_FIT);
     launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds_total, e->st);
     tk.at(LRB_T_MODEL);
-    launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds_total, e->st);
+    if (e->refine) e->kernels += launch_refine(e->K, e->ctrl, n, e->st);
+    launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds_total, e->refine, e->st);
     tk.at(LRB_T_RANSAC);
     launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st);
     e->kernels += 2 + 1 + 6 * kMaxModels + 1;
@@ -323,7 +325,8 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     e->kernels += 2 + 1 + 3;
     if (debug_sync) {
         stage(LRB_T_FIT); launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds, e->st);
-        stage(LRB_T_MODEL); launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds, e->st);
+        stage(LRB_T_MODEL); if (e->refine) e->kernels += launch_refine(e->K, e->ctrl, n, e->st);
+        launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds, e->refine, e->st);
         stage(LRB_T_RANSAC); launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st);
         stage(LRB_T_READBACK);
         order.resize(order.size() - 4);
@@ -354,6 +357,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
                 return fail(-4, "frame %d: more than %d gradient peaks (seed capacity)", i, e->S.cap);
             }
             if (C.comp_overflow || C.line_overflow) { e->prof = prof_saved; return fail(-4, "frame %d: component/segment capacity exceeded", i); }
+            if (e->refine && C.refine_overflow) { e->prof = prof_saved; return fail(-4, "frame %d: refine found more collinear segment pairs than the edge list holds", i); }
             if (C.flood_overflow) serial = true;
             else if (!C.flood_done && C.live[rounds] != 0) more_rounds = true;
             if (C.stream_overflow) more_stream = true;

@@ -78,7 +78,7 @@ __device__ __forceinline__ int block_scan_flag(int flag, int * wsum, int & total
 }
 
 // ---- K6: filter + bounding box + pencil model --------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCtrl * ctrl, float min_length, int rounds_total)
+__global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCtrl * ctrl, float min_length, int rounds_total, const float * refined, size_t refined_stride)
 {
     __shared__ int wsum[32];
     __shared__ float red[4][32];
@@ -87,9 +87,12 @@ __global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCt
     FrameCtrl & C = ctrl[slot];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const size_t ko = (size_t)slot * K.cap, lo = (size_t)slot * L.cap;
-    const int ncomp = C.n_comp;
+    // with `refine` the filter reads the merged segments (k_refine.cu); the "fewer than two raw segments" exit
+    // (interface.cpp:50-54) is taken on the unmerged count either way
+    const int ncomp = refined ? C.n_merged : C.n_comp;
     SegRec * seg = reinterpret_cast<SegRec *>(L.seg) + lo;
-    const SegRec * raw = reinterpret_cast<const SegRec *>(K.seg) + ko;
+    const SegRec * raw = refined ? reinterpret_cast<const SegRec *>(refined + (size_t)slot * refined_stride)
+                                 : reinterpret_cast<const SegRec *>(K.seg) + ko;
     const bool floods_complete = (C.live[rounds_total] == 0 || C.flood_done) && !C.flood_overflow;
     if (t == 0) {
         s_base = 0;
@@ -99,7 +102,7 @@ __global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCt
         if (floods_complete) C.fit_done = 1;             // the fit kernels ran on final floods: never redo them (they consume the owner stamps)
     }
     __syncthreads();
-    if (ncomp < 2 || !floods_complete) {                                                            // interface.cpp:50-54
+    if (C.n_comp < 2 || !floods_complete || (refined && C.refine_overflow)) {                       // interface.cpp:50-54
         if (t == 0) { C.n_lines = 0; C.num_obs = 0; }
         return;
     }
@@ -335,9 +338,9 @@ __global__ void k_finalize(Lines L, FrameCtrl * ctrl)
 
 } // namespace
 
-void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, cudaStream_t st)
+void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, bool refined, cudaStream_t st)
 {
-    k_filter_model<<<n_slots, 1024, 0, st>>>(K, L, ctrl, min_length, rounds_total);
+    k_filter_model<<<n_slots, 1024, 0, st>>>(K, L, ctrl, min_length, rounds_total, refined ? refine_output(K, 0) : nullptr, (size_t)K.cap_pool);
 }
 
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,

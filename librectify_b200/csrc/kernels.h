@@ -25,9 +25,12 @@ void launch_flood_serial(const Planes & P, const Seeds & S, const Comps & K, Fra
 void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int rounds_total, cudaStream_t st);
 void launch_labels(const Planes & P, const Comps & K, FrameCtrl * ctrl, int * labels, int slot, cudaStream_t st);
 // k6_ransac.cu
-void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, cudaStream_t st);
+void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, bool refined, cudaStream_t st);
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
                    int T, cudaStream_t st);
+// k_refine.cu
+int  launch_refine(const Comps & K, FrameCtrl * ctrl, int n_slots, cudaStream_t st);      // returns the kernels launched
+const float * refine_output(const Comps & K, int slot);                                    // merged raw segments of a slot
 // k7_sampler.cu
 void launch_sampler(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
                     int solve, int T, cudaStream_t st);

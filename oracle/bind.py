@@ -222,6 +222,14 @@ class _StageLib:
         self._f("estimate_line_pencils")(C.c_void_p(segs.ctypes.data), C.c_int(len(segs)), C.c_int(num_threads))
         return segs
 
+    def refine(self, segs):
+        """postprocess_lines_segments (reference src/line_detector.cpp:340-444) on raw segments; returns the merged list"""
+        segs = np.ascontiguousarray(segs, SEG_DTYPE)
+        out = np.zeros(len(segs), SEG_DTYPE)
+        f = self._f("refine"); f.restype = C.c_int
+        n = f(C.c_void_p(segs.ctypes.data), C.c_int(len(segs)), C.c_void_p(out.ctypes.data))
+        return out[:n].copy()
+
     def fit_line_parameters(self, X, w):
         X = np.ascontiguousarray(X, np.float32); w = np.ascontiguousarray(w, np.float32)
         out = np.zeros(1, SEG_DTYPE)

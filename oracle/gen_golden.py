@@ -80,10 +80,23 @@ def frame_case(ref: Ref, img: np.ndarray, min_length: float, full_stages: bool, 
     return out
 
 
+def refine_case(ref: Ref) -> dict:
+    """`refine` (reference src/line_detector.cpp:340-444): raw segments, their merge, and the final grouped segments"""
+    from librectify_b200.synth import manhattan_frame
+    img = manhattan_frame(11, 480, 270, n_lines=25).numpy()
+    st = ref.detect_stages(img, want_grad8=False)
+    return dict(image=img, min_length=np.float32(5.0), raw=st["segs"], merged=ref.refine(st["segs"]),
+                lines_refined=ref.find_line_segment_groups(img, 5.0, refine=True, num_threads=-1, seed=0),
+                lines_plain=ref.find_line_segment_groups(img, 5.0, refine=False, num_threads=-1, seed=0))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = Ref("canon")
     from librectify_b200.synth import manhattan_frame
+    if "--refine-only" in sys.argv:                       # added after the other fixtures were committed: leave those untouched
+        np.savez_compressed(os.path.join(GOLD, "refine.npz"), **refine_case(ref))
+        return
 
     # ---- KATs ------------------------------------------------------------------------------------------------
     kat = {}
@@ -129,6 +142,7 @@ def main():
         case.pop("image")
         case["gray_u8"] = g
         np.savez_compressed(os.path.join(GOLD, "doc_image.npz"), **case)
+    np.savez_compressed(os.path.join(GOLD, "refine.npz"), **refine_case(ref))
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

@@ -363,6 +363,72 @@ void detect(const vector<float> & im, int w, int h, Stages & S, bool keep_planes
 inline float sum3(float a, float b, float c) { return a + (b + c); }   /* Eigen unrolled redux of a fixed-size-3 vector */
 float seg_length(const Seg & l) { float x = l.x2 - l.x1, y = l.y2 - l.y1; return std::sqrt(x * x + y * y); }  /* :90-93 */
 
+/* ---- f1: `refine` post-process (ref line_detector.cpp:254-444) -------------------------------------------------------
+ * affinity (:357-401): for i < j, collinear if |d_i . d_j| >= 0.99 (double compare), the endpoints of the shorter
+ * segment, expressed in the longer one's frame (origin = its first endpoint, axes = direction / normal, scaled by its
+ * length), have |normal offset| < 0.02 (double compare) and some along-offset > -0.5 and some < 1.5.
+ * labels (:274-326): graph_components follows forward edges only (u > n), so label(u) = smallest index among the nodes
+ * with a forward path to u (u included).  merge (:254-271, :413-432): unique labels ascending, members in index order. */
+Seg merge_lines(const vector<Seg> & g)
+{
+    if (g.size() == 1) return g[0];
+    size_t k = g.size();
+    vector<float> xr(2*k), xc(2*k), w(2*k), l(k), wts(k);
+    for (size_t i = 0; i < k; ++i) {
+        l[i] = seg_length(g[i]);
+        wts[i] = l[i] * g[i].weight;                                             /* l.cwiseProduct(weights) */
+        xr[2*i] = g[i].y1; xc[2*i] = g[i].x1; xr[2*i+1] = g[i].y2; xc[2*i+1] = g[i].x2;
+        w[2*i] = wts[i]; w[2*i+1] = wts[i];
+    }
+    Seg m = fit_line_parameters(xr, xc, w);
+    float ws = wts[0], ls = l[0];
+    for (size_t i = 1; i < k; ++i) { ws = ws + wts[i]; ls = ls + l[i]; }         /* VectorXf::sum(), scalar redux */
+    m.weight = ws / ls;
+    return m;
+}
+
+bool refine_affine(const Seg & li, const Seg & lj, const float di[2], const float dj[2], float len_i, float len_j)
+{
+    float dot = di[0] * dj[0] + di[1] * dj[1];                                    /* (U^T V)(0,0) */
+    if (double(std::fabs(dot)) < 0.99) return false;
+    const Seg & S = (len_i < len_j) ? li : lj;                                   /* the segment whose endpoints are projected */
+    const Seg & L = (len_i < len_j) ? lj : li;                                   /* the frame: first endpoint, d, n, length */
+    const float * d = (len_i < len_j) ? dj : di;
+    float len = (len_i < len_j) ? len_j : len_i;
+    float nx = -d[1], ny = d[0];
+    float ax = S.x1 - L.x1, ay = S.y1 - L.y1, bx = S.x2 - L.x1, by = S.y2 - L.y1;
+    float w00 = (ax * d[0] + ay * d[1]) / len, w01 = (ax * nx + ay * ny) / len;
+    float w10 = (bx * d[0] + by * d[1]) / len, w11 = (bx * nx + by * ny) / len;
+    float off = std::max(std::fabs(w01), std::fabs(w11));
+    if (!(double(off) < 0.02)) return false;
+    return (w00 > -0.5f || w10 > -0.5f) && (w00 < 1.5f || w10 < 1.5f);
+}
+
+vector<Seg> postprocess_lines_segments(const vector<Seg> & lines)
+{
+    int n = int(lines.size());
+    vector<float> d(2 * size_t(n)), len(n);
+    for (int i = 0; i < n; ++i) {
+        float x = lines[i].x2 - lines[i].x1, y = lines[i].y2 - lines[i].y1;
+        len[i] = std::sqrt(x * x + y * y);
+        d[2*i] = x / len[i]; d[2*i+1] = y / len[i];                               /* rowwise().normalized(): no zero check */
+    }
+    vector<int> label(n);
+    for (int i = 0; i < n; ++i) label[i] = i;
+    /* forward edges only: label(j) = min(label(j), label(i)) over edges i < j, taken in increasing i (labels of i are final) */
+    for (int i = 0; i < n; ++i)
+        for (int j = i + 1; j < n; ++j)
+            if (refine_affine(lines[i], lines[j], &d[2*i], &d[2*j], len[i], len[j]) && label[i] < label[j]) label[j] = label[i];
+    vector<Seg> res;
+    for (int r = 0; r < n; ++r) {
+        if (label[r] != r) continue;
+        vector<Seg> g;
+        for (int j = r; j < n; ++j) if (label[j] == r) g.push_back(lines[j]);
+        res.push_back(merge_lines(g));
+    }
+    return res;
+}
+
 struct Model {           /* LinePencilModel ctor, ref line_pencil.cpp:25-32 on lines normalised as in :155-158 */
     int n;
     float bb[4], cx, cy, scale;
@@ -727,12 +793,13 @@ int orc_detect_stages(const float * img, int w, int h, int /*num_threads*/,
 }
 
 OrcLineSegment * find_line_segment_groups(float * buffer, int width, int height, int stride, float min_length,
-                                          bool /*refine: next-row, SURVEY §8f*/, int /*num_threads*/, int * n_lines)
+                                          bool refine, int /*num_threads*/, int * n_lines)
 {
     vector<float> im = image_from_buffer(buffer, width, height, stride);
     Stages S;
     detect(im, width, height, S, false);
     if (S.lines.size() < 2) { *n_lines = 0; return nullptr; }                       /* interface.cpp:50-54 */
+    if (refine) S.lines = postprocess_lines_segments(S.lines);                      /* interface.cpp:56-59 */
     min_length = std::max(min_length, kLineMinLength);                              /* _filter_lines interface.cpp:26-32 */
     vector<Seg> filtered;
     for (const Seg & l : S.lines) if (seg_length(l) > min_length && l.err < kLineMaxErr) filtered.push_back(l);
@@ -802,6 +869,13 @@ int orc_ransac_trace(const OrcLineSegment * lines, int n, int T, int * samples, 
     int k = estimate_line_pencils(v.data(), n, &tr);
     for (int i = 0; i < n; ++i) groups[i] = v[i].group_id;
     return k;
+}
+
+int orc_refine(const OrcLineSegment * lines, int n, OrcLineSegment * out)          /* out: capacity n; returns the merged count */
+{
+    vector<Seg> r = postprocess_lines_segments(vector<Seg>(lines, lines + n));
+    std::copy(r.begin(), r.end(), out);
+    return int(r.size());
 }
 
 void orc_fit_line_parameters(const float * X, const float * w, int n, OrcLineSegment * out)

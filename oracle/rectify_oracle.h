@@ -45,6 +45,7 @@ void orc_fit_optimal(const OrcLineSegment * lines, int n, const int * idx, int n
 long long orc_choice_knuth(unsigned seed, int n, int count, int * pairs, unsigned * next_raw);
 void orc_estimate_line_pencils(OrcLineSegment * lines, int n, int num_threads);
 void orc_fit_line_parameters(const float * X, const float * w, int n, OrcLineSegment * out);
+int  orc_refine(const OrcLineSegment * lines, int n, OrcLineSegment * out);   /* postprocess_lines_segments, line_detector.cpp:340-444 */
 void orc_compute_rectification_transform(OrcLineSegment * lines, int n, int w, int h,
                                          const OrcRectificationConfig * cfg, OrcImageTransform * out);
 void orc_compute_rectification_transform_from_vp(int w, int h, const OrcPoint * vh, const OrcPoint * vv,

@@ -219,6 +219,14 @@ void ref_estimate_line_pencils(LineSegment * lines, int n, int num_threads)
     for (int i = 0; i < n; ++i) lines[i] = v[i];
 }
 
+int ref_refine(const LineSegment * lines, int n, LineSegment * out)     /* postprocess_lines_segments, serial; out: capacity n */
+{
+    ThreadContext ctx(-1);
+    std::vector<LineSegment> r = postprocess_lines_segments(std::vector<LineSegment>(lines, lines + n), ctx);
+    for (size_t i = 0; i < r.size(); ++i) out[i] = r[i];
+    return int(r.size());
+}
+
 void ref_fit_line_parameters(const float * X /* n x 2 (row,col) */, const float * w, int n, LineSegment * out)
 {
     Eigen::MatrixX2f Xm(n, 2);
