@@ -91,9 +91,14 @@ __device__ __forceinline__ void seq_accumulate(float (*stage)[32], const float (
     for (int s = 0; s < NS; ++s) stage[s][lane] = term[s];
     __syncwarp();
     if (lane < NS) {
-        for (int k = 0; k < valid; ++k) {
-            const float t = stage[lane][k];
-            acc = (first_chunk && k == 0) ? t : __fadd_rn(acc, t);
+        // terms are fetched four at a time (the adds stay strictly sequential: that is the reference's summation order)
+        const float4 * row = reinterpret_cast<const float4 *>(stage[lane]);
+        for (int k0 = 0; k0 < valid; k0 += 4) {
+            const float4 v = row[k0 >> 2];
+            acc = (first_chunk && k0 == 0) ? v.x : __fadd_rn(acc, v.x);
+            if (k0 + 1 < valid) acc = __fadd_rn(acc, v.y);
+            if (k0 + 2 < valid) acc = __fadd_rn(acc, v.z);
+            if (k0 + 3 < valid) acc = __fadd_rn(acc, v.w);
         }
     }
     __syncwarp();
@@ -102,7 +107,8 @@ __device__ __forceinline__ void seq_accumulate(float (*stage)[32], const float (
 __global__ void __launch_bounds__(FIT_WARPS * 32)
 k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
 {
-    __shared__ float stage_all[FIT_WARPS][3][32];
+    __shared__ __align__(16) float stage_all[FIT_WARPS][3][32];
+    __shared__ float val_all[FIT_WARPS][FIT_RING];         // weights of a component that fits the ring (no re-reads from global memory)
     __shared__ unsigned ring_all[FIT_WARPS][FIT_RING];     // the last FIT_RING accepted pixels of the walk (the BFS frontier lives here)
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
@@ -111,6 +117,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float (*stage)[32] = stage_all[warp];
     unsigned * ring = ring_all[warp];
+    float * vring = val_all[warp];
     const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap, pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
     const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
@@ -143,20 +150,30 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             __stcg(owner + (size_t)sr * P.pitch + sc, listed);
         }
         __syncwarp();
+        const int pslot = lane >> 3;
+        const int ndr = kDr[lane & 7], ndc = kDc[lane & 7];                     // this lane's neighbour offset (filter.cpp:113-116 order)
         while (head < tail) {
             const int cnt = min(4, tail - head);
-            const int pslot = lane >> 3, k = lane & 7;
             const bool act = pslot < cnt;
             const int pi = head + (act ? pslot : 0);
             const unsigned prc = (tail - pi <= FIT_RING) ? ring[pi & (FIT_RING - 1)] : __ldcg(px + pi);
             head += cnt;
-            const int r = (int)(prc >> 16) + kDr[k], c = (int)(prc & 0xFFFFu) + kDc[k];
+            const int r = (int)(prc >> 16) + ndr, c = (int)(prc & 0xFFFFu) + ndc;
             const size_t po = (size_t)r * P.pitch + c;                          // parents are interior pixels: in range
-            const bool member = act && (__ldcg(owner + po) == ckey);
+            const unsigned own = __ldcg(owner + po);
+            // A pixel can be the neighbour of several of the (up to four) parents of this step; the reference's FIFO order
+            // gives it to the first of them, i.e. the lowest lane.  Two candidates coincide exactly when the pixel lies in
+            // the 3x3 neighbourhood of an earlier parent, so three shuffles (independent of the memory round trip above)
+            // replace a warp-wide match.
+            bool dup = false;
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                const unsigned o = __shfl_sync(0xffffffffu, prc, q * 8);
+                const int dr_ = r - (int)(o >> 16), dc_ = c - (int)(o & 0xFFFFu);
+                dup |= (q < pslot) && (dr_ >= -1) && (dr_ <= 1) && (dc_ >= -1) && (dc_ <= 1);
+            }
+            const bool take = act && (own == ckey) && !dup;
             const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
-            const unsigned long long mkey = member ? (unsigned long long)rcq : ((1ull << 40) | (unsigned)lane);
-            const unsigned same = __match_any_sync(0xffffffffu, mkey);
-            const bool take = member && (lane == __ffs(same) - 1);
             const unsigned tm = __ballot_sync(0xffffffffu, take);
             __syncwarp();                                                       // every lane has read its parent: ring entries may be overwritten
             if (take) {
@@ -170,6 +187,9 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
         }
         // tail == n by construction (the committed flood counted the same set)
         const int m = min(tail, n);
+        const bool small = m <= FIT_RING;                       // the whole list is still in the ring (position p at ring[p])
+#define LRB_PX(i)  (small ? ring[i] : __ldcg(px + (i)))
+#define LRB_VAL(i) (small ? vring[i] : val[i])
 
         // ---- fit_line_parameters (geometry.cpp:20-61); X = (row, col), weights = G_b ------------------------------
         float acc = 0.f;
@@ -178,10 +198,11 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             const int i = i0 + lane; const int valid = min(32, m - i0);
             float t[1] = {0.f};
             if (i < m) {
-                const unsigned rc = __ldcg(px + i);
+                const unsigned rc = LRB_PX(i);
                 const size_t po = (size_t)(rc >> 16) * P.pitch + (rc & 0xFFFFu);
                 t[0] = orient_energy(__ldg(dx + po), __ldg(dy + po), b);
                 val[i] = t[0];
+                if (small) vring[i] = t[0];
             }
             seq_accumulate<1>(stage, t, valid, lane, i0 == 0, acc);
         }
@@ -193,8 +214,8 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             const int i = i0 + lane; const int valid = min(32, m - i0);
             float t[2] = {0.f, 0.f};
             if (i < m) {
-                const unsigned rc = __ldcg(px + i);
-                const float wt = __fdiv_rn(val[i], wsum);
+                const unsigned rc = LRB_PX(i);
+                const float wt = __fdiv_rn(LRB_VAL(i), wsum);
                 t[0] = __fmul_rn((float)(rc >> 16), wt); t[1] = __fmul_rn((float)(rc & 0xFFFFu), wt);
             }
             seq_accumulate<2>(stage, t, valid, lane, i0 == 0, acc);
@@ -206,8 +227,8 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             const int i = i0 + lane; const int valid = min(32, m - i0);
             float t[3] = {0.f, 0.f, 0.f};
             if (i < m) {
-                const unsigned rc = __ldcg(px + i);
-                const float wt = __fdiv_rn(val[i], wsum);
+                const unsigned rc = LRB_PX(i);
+                const float wt = __fdiv_rn(LRB_VAL(i), wsum);
                 const float c0 = __fsub_rn((float)(rc >> 16), a0), c1 = __fsub_rn((float)(rc & 0xFFFFu), a1);
                 t[0] = __fmul_rn(__fmul_rn(c0, wt), c0);       // cov(0,0)
                 t[1] = __fmul_rn(__fmul_rn(c1, wt), c0);       // cov(1,0)
@@ -229,7 +250,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             const int i = i0 + lane; const int valid = min(32, m - i0);
             float t[1] = {0.f};
             if (i < m) {
-                const unsigned rc = __ldcg(px + i);
+                const unsigned rc = LRB_PX(i);
                 const float c0 = __fsub_rn((float)(rc >> 16), a0), c1 = __fsub_rn((float)(rc & 0xFFFFu), a1);
                 const float tt = __fadd_rn(__fmul_rn(c0, d0), __fmul_rn(c1, d1));
                 tmin = fminf(tmin, tt); tmax = fmaxf(tmax, tt);
@@ -251,6 +272,8 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             s.group_id = -1;
             reinterpret_cast<SegRec *>(K.seg)[ko + comp] = s;
         }
+#undef LRB_PX
+#undef LRB_VAL
         __syncwarp();
     }
 }

@@ -29,7 +29,7 @@ constexpr int RF_TILE = 256;
 struct RefineScratch {
     float * dx; float * dy; float * len;    // unit direction and length per raw segment
     int * label; int * cnt; int * rrank;    // label, members per root, output position of a root
-    int * multi;                            // indices of segments in multi-member groups, ascending
+    int * multi; int * goff; int * fill;    // member lists of the multi-member groups (contiguous per group, ascending), their offsets
     SegRec * out;                           // merged segments (read by k_filter_model)
     int * edges; int edge_cap;              // (i, j) pairs
 };
@@ -41,9 +41,10 @@ __device__ __host__ __forceinline__ RefineScratch refine_scratch(const Comps & K
     const size_t c = (size_t)K.cap;
     R.dx = reinterpret_cast<float *>(base); R.dy = R.dx + c; R.len = R.dy + c;
     R.label = reinterpret_cast<int *>(base + 3 * c); R.cnt = R.label + c; R.rrank = R.cnt + c; R.multi = R.rrank + c;
-    R.out = reinterpret_cast<SegRec *>(base + 7 * c);
-    R.edges = reinterpret_cast<int *>(base + 14 * c);
-    const long long left = (long long)K.cap_pool - 14ll * (long long)c;
+    R.goff = R.multi + c; R.fill = R.goff + c;
+    R.out = reinterpret_cast<SegRec *>(base + 9 * c);
+    R.edges = reinterpret_cast<int *>(base + 16 * c);
+    const long long left = (long long)K.cap_pool - 16ll * (long long)c;
     R.edge_cap = (int)(left > 0 ? left / 2 : 0);
     return R;
 }
@@ -61,34 +62,45 @@ __global__ void __launch_bounds__(256) k_refine_prep(Comps K, FrameCtrl * ctrl)
         const float x = __fsub_rn(s.x2, s.x1), y = __fsub_rn(s.y2, s.y1);                     // geometry.cpp:76-79
         const float l = __fsqrt_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)));             // rowwise().norm()
         R.dx[i] = __fdiv_rn(x, l); R.dy[i] = __fdiv_rn(y, l); R.len[i] = l;                   // rowwise().normalized(): no zero check
-        R.label[i] = i; R.cnt[i] = 0;
+        R.label[i] = i; R.cnt[i] = 0; R.fill[i] = 0;
     }
 }
 
-// line_detector.cpp:372-401 for one pair; (ax..) = segment i, (bx..) = segment j
+// The reference compares floats against the double literals 0.99 and 0.02 (line_detector.cpp:377,391).  For a float x,
+// x < 0.99 (as double) <=> x < kCosLimit with kCosLimit the smallest float >= 0.99 (no float lies in between); same for 0.02.
+constexpr float kCosLimit = 0x1.fae148p-1f, kOffsetLimit = 0x1.47ae16p-6f;
+static_assert((double)kCosLimit >= 0.99 && (double)0x1.fae146p-1f < 0.99, "kCosLimit is not the float successor of 0.99");
+static_assert((double)kOffsetLimit >= 0.02 && (double)0x1.47ae14p-6f < 0.02, "kOffsetLimit is not the float successor of 0.02");
+
+// line_detector.cpp:378-401 for one pair that passed the cosine test; (ix..) = segment i, (jx..) = segment j
 __device__ __forceinline__ bool refine_affine(float ix1, float iy1, float ix2, float iy2, float idx, float idy, float il,
                                               float jx1, float jy1, float jx2, float jy2, float jdx, float jdy, float jl)
 {
-    const float dot = __fadd_rn(__fmul_rn(idx, jdx), __fmul_rn(idy, jdy));                  // (U^T V)(0,0)
-    if ((double)fabsf(dot) < 0.99) return false;
     const bool i_short = il < jl;                                                           // project the shorter one
     const float sx1 = i_short ? ix1 : jx1, sy1 = i_short ? iy1 : jy1, sx2 = i_short ? ix2 : jx2, sy2 = i_short ? iy2 : jy2;
     const float ox = i_short ? jx1 : ix1, oy = i_short ? jy1 : iy1;
     const float dx = i_short ? jdx : idx, dy = i_short ? jdy : idy, len = i_short ? jl : il;
     const float nx = -dy, ny = dx;
-    const float ax = __fsub_rn(sx1, ox), ay = __fsub_rn(sy1, oy), bx = __fsub_rn(sx2, ox), by = __fsub_rn(sy2, oy);
+    const float ax = __fsub_rn(sx1, ox), ay = __fsub_rn(sy1, oy);
+    // cheap conservative reject before the four IEEE divisions: |n01| >= 1.01 * 0.02 * len implies |n01 / len| >= 0.02
+    // whatever the roundings (each is below 1e-6 relative); parallel but distant segments — most pairs that pass the
+    // cosine test in a Manhattan scene — leave here
+    const float n01 = __fadd_rn(__fmul_rn(ax, nx), __fmul_rn(ay, ny));
+    if (fabsf(n01) >= __fmul_rn(1.01f * kOffsetLimit, len)) return false;
+    const float bx = __fsub_rn(sx2, ox), by = __fsub_rn(sy2, oy);
     const float w00 = __fdiv_rn(__fadd_rn(__fmul_rn(ax, dx), __fmul_rn(ay, dy)), len);
-    const float w01 = __fdiv_rn(__fadd_rn(__fmul_rn(ax, nx), __fmul_rn(ay, ny)), len);
+    const float w01 = __fdiv_rn(n01, len);
     const float w10 = __fdiv_rn(__fadd_rn(__fmul_rn(bx, dx), __fmul_rn(by, dy)), len);
     const float w11 = __fdiv_rn(__fadd_rn(__fmul_rn(bx, nx), __fmul_rn(by, ny)), len);
-    if (!((double)fmaxf(fabsf(w01), fabsf(w11)) < 0.02)) return false;
+    if (!(fmaxf(fabsf(w01), fabsf(w11)) < kOffsetLimit)) return false;
     return (w00 > -0.5f || w10 > -0.5f) && (w00 < 1.5f || w10 < 1.5f);
 }
 
 // all pairs i < j: tile pairs (bi <= bj) are handed out over the grid; thread t of a block owns i = bi*RF_TILE + t
 __global__ void __launch_bounds__(RF_TILE) k_refine_edges(Comps K, FrameCtrl * ctrl)
 {
-    __shared__ float sj[7][RF_TILE];
+    __shared__ float2 sd[RF_TILE];              // unit directions of the j tile (all that ~99.9 % of the pairs ever need)
+    __shared__ float sj[5][RF_TILE];
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     const int n = C.n_comp;
@@ -106,8 +118,8 @@ __global__ void __launch_bounds__(RF_TILE) k_refine_edges(Comps K, FrameCtrl * c
             const int j = j0 + t;
             if (j < n) {
                 const SegRec s = raw[j];
-                sj[0][t] = s.x1; sj[1][t] = s.y1; sj[2][t] = s.x2; sj[3][t] = s.y2;
-                sj[4][t] = R.dx[j]; sj[5][t] = R.dy[j]; sj[6][t] = R.len[j];
+                sj[0][t] = s.x1; sj[1][t] = s.y1; sj[2][t] = s.x2; sj[3][t] = s.y2; sj[4][t] = R.len[j];
+                sd[t] = make_float2(R.dx[j], R.dy[j]);
             }
         }
         __syncthreads();
@@ -116,8 +128,11 @@ __global__ void __launch_bounds__(RF_TILE) k_refine_edges(Comps K, FrameCtrl * c
         const float idx = R.dx[i], idy = R.dy[i], il = R.len[i];
         const int jn = min(RF_TILE, n - j0);
         for (int k = (bi == bj) ? t + 1 : 0; k < jn; ++k) {
+            const float2 dj = sd[k];
+            const float dot = __fadd_rn(__fmul_rn(idx, dj.x), __fmul_rn(idy, dj.y));        // (U^T V)(0,0), line_detector.cpp:377
+            if (fabsf(dot) < kCosLimit) continue;
             if (refine_affine(si.x1, si.y1, si.x2, si.y2, idx, idy, il,
-                              sj[0][k], sj[1][k], sj[2][k], sj[3][k], sj[4][k], sj[5][k], sj[6][k])) {
+                              sj[0][k], sj[1][k], sj[2][k], sj[3][k], dj.x, dj.y, sj[4][k])) {
                 const int e = atomicAdd(&C.n_edges, 1);
                 if (e < R.edge_cap) { R.edges[2 * e] = i; R.edges[2 * e + 1] = j0 + k; }
                 else C.refine_overflow = 1;
@@ -147,16 +162,37 @@ __device__ __forceinline__ int scan_flag_1024(int flag, int * wsum, int & total)
     return pos;
 }
 
-// merge_lines (line_detector.cpp:254-271) for root r: members = multi[] entries whose label is r, in index order.
+// exclusive block scan of a value over 1024 threads, total in `total`
+__device__ __forceinline__ int scan_val_1024(int v, int * wsum, int & total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { const int u = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += u; }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = wsum[lane];
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { const int u = __shfl_up_sync(0xffffffffu, w, s); if (lane >= s) w += u; }
+        wsum[lane] = w;
+    }
+    __syncthreads();
+    const int pos = inc - v + (warp ? wsum[warp - 1] : 0);
+    total = wsum[31];
+    __syncthreads();
+    return pos;
+}
+
+// merge_lines (line_detector.cpp:254-271) for root r: members = mem[0..km), in index order.
 // fit_line_parameters (geometry.cpp:20-61) on the 2k endpoints (row, col) = (y, x) with weights length*weight, every
 // sum sequential in member order — the same arithmetic as k5_fit.cu, one thread per group (groups are few and small).
-__device__ void merge_group(const SegRec * raw, const RefineScratch & R, int n_multi, int r, SegRec & out)
+__device__ void merge_group(const SegRec * raw, const RefineScratch & R, const int * mem, int km, SegRec & out)
 {
     // pass 1: weights and their sums
     float wsum = 0.f, ws = 0.f, ls = 0.f; int k = 0;
-    for (int q = 0; q < n_multi; ++q) {
-        const int u = R.multi[q];
-        if (R.label[u] != r) continue;
+    for (int q = 0; q < km; ++q) {
+        const int u = mem[q];
         const float l = R.len[u];
         const float w = __fmul_rn(l, raw[u].weight);                                        // l.cwiseProduct(weights)
         wsum = (k == 0) ? w : __fadd_rn(wsum, w);  wsum = __fadd_rn(wsum, w);               // W(2i) and W(2i+1)
@@ -167,9 +203,8 @@ __device__ void merge_group(const SegRec * raw, const RefineScratch & R, int n_m
     const int np = 2 * k;
     // pass 2: weighted mean a = sum X * (w / wsum)
     float a0 = 0.f, a1 = 0.f; bool first = true;
-    for (int q = 0; q < n_multi; ++q) {
-        const int u = R.multi[q];
-        if (R.label[u] != r) continue;
+    for (int q = 0; q < km; ++q) {
+        const int u = mem[q];
         const SegRec s = raw[u];
         const float wt = __fdiv_rn(__fmul_rn(R.len[u], s.weight), wsum);
         const float t0 = __fmul_rn(s.y1, wt), t1 = __fmul_rn(s.x1, wt), t2 = __fmul_rn(s.y2, wt), t3 = __fmul_rn(s.x2, wt);
@@ -178,9 +213,8 @@ __device__ void merge_group(const SegRec * raw, const RefineScratch & R, int n_m
     }
     // pass 3: lower triangle of centered^T diag(wt) centered: (c_i * wt) * c_j
     float c00 = 0.f, c10 = 0.f, c11 = 0.f; first = true;
-    for (int q = 0; q < n_multi; ++q) {
-        const int u = R.multi[q];
-        if (R.label[u] != r) continue;
+    for (int q = 0; q < km; ++q) {
+        const int u = mem[q];
         const SegRec s = raw[u];
         const float wt = __fdiv_rn(__fmul_rn(R.len[u], s.weight), wsum);
 #pragma unroll
@@ -196,9 +230,8 @@ __device__ void merge_group(const SegRec * raw, const RefineScratch & R, int n_m
     const float d0 = evec[2], d1 = evec[3], n0 = evec[0], n1 = evec[1];                    // column 1 = direction, column 0 = normal
     // pass 4: projection range and mean |normal residual|
     float tmin = INFINITY, tmax = -INFINITY, esum = 0.f; first = true;
-    for (int q = 0; q < n_multi; ++q) {
-        const int u = R.multi[q];
-        if (R.label[u] != r) continue;
+    for (int q = 0; q < km; ++q) {
+        const int u = mem[q];
         const SegRec s = raw[u];
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
@@ -261,24 +294,38 @@ __global__ void __launch_bounds__(1024) k_refine_merge(Comps K, FrameCtrl * ctrl
     }
     const int n_roots = s_base;
     __syncthreads();
+    // member lists of the multi-member groups: offsets by an ordered scan over the roots, unordered fill, then every
+    // group's (short) list is put into index order by its own thread
     if (t == 0) s_base = 0;
     __syncthreads();
     for (int u0 = 0; u0 < n; u0 += 1024) {
         const int u = u0 + t;
-        const int flag = (u < n) && (R.cnt[R.label[u]] > 1);
-        int total; const int pos = s_base + scan_flag_1024(flag, wsum, total);
-        if (flag) R.multi[pos] = u;
+        const int v = (u < n && R.label[u] == u && R.cnt[u] > 1) ? R.cnt[u] : 0;
+        int total; const int pos = s_base + scan_val_1024(v, wsum, total);
+        if (v) R.goff[u] = pos;
         if (t == 0) s_base += total;
         __syncthreads();
     }
-    const int n_multi = s_base;
+    for (int u = t; u < n; u += 1024) {
+        const int r = R.label[u];
+        if (R.cnt[r] > 1) R.multi[R.goff[r] + atomicAdd(&R.fill[r], 1)] = u;
+    }
     __syncthreads();
     // ---- merged segments (std::set order = ascending root index) ---------------------------------------------------------
     for (int u = t; u < n; u += 1024) {
         if (R.label[u] != u) continue;
         SegRec o;
-        if (R.cnt[u] == 1) o = raw[u];                                                      // line_detector.cpp:256-257
-        else merge_group(raw, R, n_multi, u, o);
+        const int km = R.cnt[u];
+        if (km == 1) o = raw[u];                                                            // line_detector.cpp:256-257
+        else {
+            int * mem = R.multi + R.goff[u];
+            for (int a = 1; a < km; ++a) {                                                  // insertion sort, ascending index
+                const int v = mem[a]; int b2 = a - 1;
+                while (b2 >= 0 && mem[b2] > v) { mem[b2 + 1] = mem[b2]; --b2; }
+                mem[b2 + 1] = v;
+            }
+            merge_group(raw, R, mem, km, o);
+        }
         R.out[R.rrank[u]] = o;
     }
     if (t == 0) C.n_merged = n_roots;

@@ -8,7 +8,8 @@ src, dst, title = sys.argv[1], sys.argv[2], sys.argv[3]
 lines = [l for l in open(src) if not l.startswith("==")]
 agg = collections.OrderedDict()
 for row in csv.DictReader(lines):
-    name = re.sub(r"\(.*", "", row["Kernel Name"]).replace("void ", "").replace("lrb::<unnamed>::", "")
+    m = re.search(r"\b(k_[a-z0-9_]+)", row["Kernel Name"])
+    name = m.group(1) if m else re.sub(r"\(.*", "", row["Kernel Name"])
     v = float(row["Metric Value"].replace(",", ""))
     v = v / 1000 if row["Metric Unit"] == "ns" else (v * 1000 if row["Metric Unit"] == "ms" else v)
     a = agg.setdefault(name, [0, 0.0, row["Grid Size"], row["Block Size"]])
