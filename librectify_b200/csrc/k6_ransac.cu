@@ -167,6 +167,10 @@ __global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCt
     }
 }
 
+// decision thresholds of the fast inlier test in k_score: (1 - tol +- 4e-6)^2, evaluated in double
+constexpr double kInTheta = 1.0 - (double)kTolInlier;
+constexpr float kInHi = (float)((kInTheta + 4e-6) * (kInTheta + 4e-6)), kInLo = (float)((kInTheta - 4e-6) * (kInTheta - 4e-6));
+
 // ---- K8: scoring grid -------------------------------------------------------------------------------------------------
 constexpr int SC_THREADS = 128;
 constexpr int SC_CHUNK = 1024;
@@ -211,9 +215,17 @@ __global__ void __launch_bounds__(SC_THREADS) k_score(Lines L, FrameCtrl * ctrl,
 #pragma unroll 4
             for (int k = 0; k < cn; ++k) {
                 const float4 v = s_ad[k];
-                const float e = line_error(h, v.x, v.y, v.z, v.w);
-                const float tt = __fmul_rn(e < kTolInlier ? 1.f : 0.f, s_len[k]);       // line_pencil.cpp:137-140
-                score = (c0 + k == 0) ? tt : __fadd_rn(score, tt);
+                // inlier <=> 1 - |v^ . d| < tol (line_pencil.cpp:137-140).  Only this boolean enters the score, and for
+                // all but a ~1e-5 sliver of pairs it is decided without the IEEE sqrt and the two divisions:
+                // (v.d)^2 against |v|^2 (1 - tol -+ delta)^2, delta = 4e-6 — five times the worst-case sum of the
+                // rounding errors of both evaluations — the sliver takes the exact path.
+                const float vx = h.ideal ? h.px : __fadd_rn(-v.x, h.px), vy = h.ideal ? h.py : __fadd_rn(-v.y, h.py);
+                const float D = __fadd_rn(__fmul_rn(vx, v.z), __fmul_rn(vy, v.w));
+                const float Z = __fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy));
+                const float D2 = __fmul_rn(D, D);
+                bool in = D2 > __fmul_rn(Z, kInHi);
+                if (!in && !(D2 < __fmul_rn(Z, kInLo))) in = line_error(h, v.x, v.y, v.z, v.w) < kTolInlier;
+                if (in) score = __fadd_rn(score, s_len[k]);                  // adding the +0 of an outlier changes nothing
             }
         }
     }
