@@ -169,12 +169,23 @@ __device__ __forceinline__ int flood_tiles(const FloodCtx & X, const TileTab & T
         __syncwarp();
         if (lane == 0) T.dirty[e] = 0;
         unsigned hz;
-        while (true) {                                                      // fixed point of R <- E & dilate(R)
-            hz = R | (R << 1) | (R >> 1);
+        // Fixed point of R <- E & dilate(R).  Inside a row the flood is completed in one go with the carry trick: for
+        // R within E, ((E + R) ^ E) & E | R is R extended to the upper end of every run of E it touches (the carry of the
+        // addition ripples through the run); the same on the bit-reversed words extends downwards.  An iteration is then
+        // one complete horizontal fill plus one step to the rows above and below, so a near-horizontal line takes a
+        // handful of iterations instead of one per pixel of its length.
+        const unsigned Erev = __brev(E);
+        while (true) {
+            const unsigned s1 = E + R;
+            const unsigned f1 = ((s1 ^ E) & E) | R;
+            const unsigned r1 = __brev(f1);
+            const unsigned s2 = Erev + r1;
+            const unsigned H = __brev(((s2 ^ Erev) & Erev) | r1);              // R, horizontally closed
+            hz = H | (H << 1) | (H >> 1);
             unsigned up = __shfl_up_sync(0xffffffffu, hz, 1), dn = __shfl_down_sync(0xffffffffu, hz, 1);
             if (lane == 0) up = 0u;
             if (lane == 31) dn = 0u;
-            const unsigned Rn = R | (E & (hz | up | dn));
+            const unsigned Rn = H | (E & (up | dn));
             const bool ch = __any_sync(0xffffffffu, Rn != R);
             R = Rn; ++dbg[1];
             if (!ch) break;
