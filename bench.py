@@ -92,7 +92,7 @@ def make_frames(rank, n, device):
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
-        return 0
+        return None
     from oracle.bind import Ref, RectificationConfig, ref_available
     import torch
     cores = os.cpu_count() or 1
@@ -129,8 +129,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
-    return 0
+    return line
 
 
 # ---- this repo's arm ----------------------------------------------------------------------------------------------------
@@ -273,14 +272,12 @@ def run_b200(args):
         "device_vs_host_results_identical": same,
         "clocks": clk.summary(),
     }
-    if rank == 0:
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_sample()
-        print(json.dumps(line))
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_sample()
     runner.close()
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return line if rank == 0 else None
 
 
 def main():
@@ -295,9 +292,22 @@ def main():
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm (bounded CPU sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    if args.impl == "reference":
-        return run_reference(args)
-    return run_b200(args)
+    # torchrun exports OMP_NUM_THREADS=1, which would throttle the reference's OpenMP path (threading.h:24-31 clamps to
+    # omp_get_max_threads()): the CPU arms use all host cores, so say so before any OpenMP runtime starts
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+    # the contract is ONE JSON line on stdout: libraries that print there (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        line = run_reference(args) if args.impl == "reference" else run_b200(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    return 0
 
 
 if __name__ == "__main__":
