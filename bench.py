@@ -286,7 +286,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames", type=int, default=128, help="frames per GPU per step")
+    ap.add_argument("--frames", type=int, default=256, help="frames per GPU per step")
     ap.add_argument("--engines", type=int, default=4, help="engines (streams + workspaces) per GPU")
     ap.add_argument("--slots", type=int, default=32, help="frame slots per engine (frames per launch group)")
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm (bounded CPU sample)")

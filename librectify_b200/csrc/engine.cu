@@ -85,6 +85,9 @@ constexpr int kBigSlots = 64;          // concurrent long floods (global-memory 
 struct lrb_engine {
     int device = 0, slots = 1;
     cudaStream_t st = nullptr;
+    // host input: the next group's frames are copied on a second stream as soon as K1 of the current group has consumed
+    // the image workspace, so the copy overlaps flood / fit / RANSAC of the current group
+    cudaStream_t st_copy = nullptr; cudaEvent_t ev_k1_done = nullptr, ev_copy_done = nullptr; bool pre_copied = false;
     // workspace geometry
     int w = 0, h = 0, pitch = 0;
     size_t plane = 0;                  // elements per slot plane
@@ -256,10 +259,21 @@ void collect_profile(lrb_engine * e, const std::vector<int> & order)
 }
 
 int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w, int h, long long pitch,
-              long long fstride, float min_length);
+              long long fstride, float min_length, int n_next);
 
+void copy_host_frames(lrb_engine * e, const float * frames, int n, int w, int h, long long pitch, long long fstride, cudaStream_t st)
+{
+    for (int i = 0; i < n; ++i) {
+        const float * base = frames + (long long)i * fstride; long long p = pitch;
+        if (p < 0) { base = base + (long long)(h - 1) * p; p = -p; }
+        cudaMemcpy2DAsync(e->ws_img + (size_t)i * e->plane, sizeof(float) * e->pitch, base, sizeof(float) * (size_t)p,
+                          sizeof(float) * w, h, cudaMemcpyHostToDevice, st);
+    }
+}
+
+// n_next > 0: the n_next frames that follow this group in the caller's host buffer form the next group (host input only)
 int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w, int h, long long pitch,
-              long long fstride, float min_length)
+              long long fstride, float min_length, int n_next)
 {
     if (n < 1 || n > e->slots) return fail(-1, "group of %d frames does not fit %d slots", n, e->slots);
     CK(cudaSetDevice(e->device));
@@ -304,17 +318,24 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
             if (p < 0) { base = frames + (long long)(h - 1) * p; p = -p; }
             launch_ingest(base, p, fstride, e->ws_img, e->pitch, e->plane, w, h, n, e->st); e->kernels++;
         }
+    } else if (e->pre_copied) {
+        CK(cudaStreamWaitEvent(e->st, e->ev_copy_done, 0));              // copied while the previous group was computing
+        e->pre_copied = false;
     } else {
-        for (int i = 0; i < n; ++i) {
-            const float * base = frames + (long long)i * fstride; long long p = pitch;
-            if (p < 0) { base = base + (long long)(h - 1) * p; p = -p; }
-            CK(cudaMemcpy2DAsync(e->ws_img + (size_t)i * e->plane, sizeof(float) * e->pitch, base, sizeof(float) * (size_t)p,
-                                 sizeof(float) * w, h, cudaMemcpyHostToDevice, e->st));
-        }
+        copy_host_frames(e, frames, n, w, h, pitch, fstride, e->st);
+        CK(cudaGetLastError());
     }
     // ---- detection ---------------------------------------------------------------------------------------------------
     stage(LRB_T_GRAD);
     launch_grad(*tm, P1, e->ctrl, n, tma_x, tma_y, e->st);
+    static const bool no_prefetch = getenv("LRB_NO_PREFETCH") != nullptr;
+    if (!on_device && n_next > 0 && !no_prefetch) {                       // the image workspace is free again after K1
+        CK(cudaEventRecord(e->ev_k1_done, e->st));
+        CK(cudaStreamWaitEvent(e->st_copy, e->ev_k1_done, 0));
+        copy_host_frames(e, frames + (long long)n * fstride, n_next, w, h, pitch, fstride, e->st_copy);
+        CK(cudaEventRecord(e->ev_copy_done, e->st_copy));
+        e->pre_copied = true;
+    }
     stage(LRB_T_NMS);
     launch_nms(e->tm_mag, e->tm_bin, e->P, e->S, e->ctrl, n, kMarginX, kMarginY, e->st);
     stage(LRB_T_SEEDS);
@@ -352,7 +373,8 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
                 e->prof = prof_saved;
                 if (e->seed_div > 1) {                    // plateau-like input: every pixel can be a peak; enlarge the seed arrays once
                     e->seed_div = 1;
-                    return run_group(e, frames, on_device, n, w, h, pitch, fstride, min_length);
+                    if (e->pre_copied) { CK(cudaStreamSynchronize(e->st_copy)); e->pre_copied = false; }   // the workspace is rebuilt: copy again
+                    return run_group(e, frames, on_device, n, w, h, pitch, fstride, min_length, n_next);
                 }
                 return fail(-4, "frame %d: more than %d gradient peaks (seed capacity)", i, e->S.cap);
             }
@@ -409,7 +431,11 @@ int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, i
     std::vector<lrb_segment> tmp;
     for (int f0 = 0; f0 < n_frames; f0 += e->slots) {
         const int n = std::min(e->slots, n_frames - f0);
-        if (int r = run_group(e, frames + (long long)f0 * fstride, on_device, n, w, h, pitch, fstride, min_length)) return r;
+        const int n_next = std::min(e->slots, n_frames - f0 - n);
+        if (int r = run_group(e, frames + (long long)f0 * fstride, on_device, n, w, h, pitch, fstride, min_length, n_next)) {
+            if (e->pre_copied) { cudaStreamSynchronize(e->st_copy); e->pre_copied = false; }
+            return r;
+        }
         for (int i = 0; i < n; ++i) {
             const int nl = e->h_ctrl[i].n_lines;
             if (info) fill_info(e, i, &info[f0 + i]);

@@ -254,6 +254,26 @@ def test_batch_device_frames_match_single(api, oracle):
     e1.close(); e4.close()
 
 
+def test_host_batch_longer_than_the_slots(api, oracle):
+    """host frames in several launch groups: the next group's host->device copy is issued on a second stream while the
+    current group computes; pinned and pageable memory, group sizes 2+2+1, results == per-frame oracle"""
+    import torch
+    from librectify_b200.synth import manhattan_frame
+    frames = torch.stack([manhattan_frame(40 + i, 640, 360, n_lines=30) for i in range(5)])   # frames without exact-magnitude seed ties
+    pinned = torch.empty(frames.shape, dtype=torch.float32, pin_memory=True); pinned.copy_(frames)
+    e2 = api.Engine(0, 2)
+    ref = [oracle.find_line_segment_groups(frames[i].numpy(), 6.4, seed=0) for i in range(5)]
+    for src in (pinned.numpy(), frames.numpy().copy()):
+        for _ in range(2):                                     # twice: the prefetch state must not leak between calls
+            _, lines = e2.detect(src, 6.4)
+            for i in range(5):
+                assert lines[i].tobytes() == ref[i].tobytes(), i
+    tf, _ = e2.rectify(pinned.numpy(), 6.4)
+    for i in range(5):
+        assert np.array_equal(api.tform_vec(tf[i]), api.tform_vec(api.compute_rectification_transform(ref[i], 640, 360)), equal_nan=True)
+    e2.close()
+
+
 def test_idempotent_and_workspace_reuse(api, eng):
     """the epoch-stamped ownership plane is reused across frames and sizes without clearing: results must not depend on history"""
     a = _synth(50, 800, 450, n_lines=30); b = _synth(51, 640, 360, n_lines=30)
