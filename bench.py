@@ -263,7 +263,7 @@ def run_b200(args):
         "gpu_launches": int(prof["kernels"]),
         "roofline": {"kernel": "k_grad5x5_bin (K1)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak if peak else None, "traffic": K1_NCU_DRAM_BYTES_PER_PX * W * H * frames_per_launch,
-                     "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one 8-frame launch (profiles/r1_k1_full.md), scaled to this launch size", "peak_source": peak_src,
+                     "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one 8-frame launch (profiles/r1_ncu_full_final.md), scaled to this launch size", "peak_source": peak_src,
                      "algorithmic_bytes_per_px": K1_BYTES_PER_PX, "frames_per_launch": frames_per_launch, "ms_per_launch": k1_ms,
                      "k2_nms_GBps": (K2_BYTES_PER_PX * W * H * frames_per_launch / (k2_ms * 1e-3) / 1e9) if k2_ms > 0 else None},
         "stage_ms_per_frame": stage_ms_per_frame,
