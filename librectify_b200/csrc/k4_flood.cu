@@ -76,7 +76,7 @@ __device__ __forceinline__ unsigned bits_of_bytes(const uint4 & a, const uint4 &
 // Returns (visited bitmap << 32) | eligible bitmap.  RB = rows whose dx/dy loads are in flight together (16: two dependent
 // batches, 64 live registers less; 32: a single batch).
 template <int RB>
-__device__ __noinline__ unsigned long long tile_eligible(const FloodCtx X, int y0, int x0, int lane)
+__device__ __forceinline__ unsigned long long tile_eligible(const FloodCtx X, int y0, int x0, int lane)
 {
     // (1) mask / visited bytes of this lane's row, two 16-byte halves each
     const int y = y0 + lane;
@@ -553,7 +553,7 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
     // flood: a resident set of CTAs per frame, warps pull seeds from the frame's queue; verify: warps striding over the window
     // register budget of the flood kernel: MINB resident CTAs per SM (LRB_FLOOD_MINB=4|5|6|8 for experiments; 4 loads a tile's 32 rows in one batch)
     static const int minb = [] { const char * v = getenv("LRB_FLOOD_MINB"); return v ? atoi(v) : 4; }();
-    auto kern = (minb >= 8) ? k_flood_round<8, 16> : (minb == 6) ? k_flood_round<6, 16> : (minb == 4) ? k_flood_round<4, 32> : k_flood_round<5, 16>;
+    auto kern = (minb >= 8) ? k_flood_round<8, 16> : (minb == 6) ? k_flood_round<6, 16> : (minb == 4) ? k_flood_round<4, 32> : (minb == 7) ? k_flood_round<6, 32> : (minb == 3) ? k_flood_round<5, 32> : k_flood_round<5, 16>;
     static int per_sm = 0;
     if (per_sm == 0) {
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FL_WARPS * 32, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
