@@ -215,6 +215,14 @@ def run_b200(args):
     def step_host():
         out["tf_h"], out["info_h"] = runner.rectify(frames_host.numpy(), MIN_LENGTH, cfg)
 
+    # the same frames quantised to 8 bits, for the device-ingest entry point (lrb_rectify_host_u8):
+    # 1 byte per pixel over PCIe instead of 4.  Reported as an extra; the headline e2e stays the float call.
+    frames_u8 = torch.empty((B, H, W), dtype=torch.uint8, pin_memory=True)
+    frames_u8.copy_((frames_dev * 256.0).clamp_(0, 255).to(torch.uint8))
+
+    def step_host_u8():
+        out["tf_u8"], _ = runner.rectify(frames_u8.numpy(), MIN_LENGTH, cfg, u8=True)
+
     for _ in range(max(args.warmup, 3)):
         step_dev()
     runner.profile(True)
@@ -225,6 +233,9 @@ def run_b200(args):
     for _ in range(2):
         step_host()
     sec_e2e = timed(step_host, args.steps)
+    for _ in range(2):
+        step_host_u8()
+    sec_e2e_u8 = timed(step_host_u8, args.steps)
 
     # single-frame latency (BASELINE config 2): one frame, one engine, device-resident, p50 over 30 calls
     lat = []
@@ -259,6 +270,8 @@ def run_b200(args):
                    "l2": f"inputs {B * W * H * 4 / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)", "parallelism": f"frames sharded over {world} GPU(s), no collective"},
         "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(B * W * H * 4),
                 "d2h_bytes_per_step": int(out["info"].nbytes + sum(int(n) for n in info["n_lines"]) * 28 + B * 640)},
+        "e2e_u8": {"value": n_total / sec_e2e_u8, "unit": "images/s", "h2d_bytes_per_step": int(B * W * H),
+                   "note": "same frames quantised to 8-bit gray, lrb_rectify_host_u8 (gray/256 on the device); extra, not the headline"},
         "latency_ms_p50_single_frame": lat_p50,
         "gpu_launches": int(prof["kernels"]),
         "roofline": {"kernel": "k_grad5x5_bin (K1)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -82,6 +82,23 @@ LRB_API int lrb_detect_host(lrb_engine * e, const float * frames, int n_frames, 
                             long long pitch, long long frame_stride, float min_length,
                             lrb_frame_info * info, lrb_segment * lines, int lines_cap);
 
+/* 8-bit frames: what the reference's demo does on the CPU before it calls the library —
+ * cv::cvtColor(BGR2GRAY) (src/autorectify.cpp:340) and convertTo(CV_32F, 1/256.0) (src/autorectify.cpp:119) — moved to
+ * the device, so a host caller ships 1 (gray) or 3 (BGR) bytes per pixel over PCIe instead of 4.  channels: 1 or 3;
+ * pitch and frame_stride are in BYTES.  The result is bit-identical to passing the float frame gray/256. */
+LRB_API int lrb_detect_host_u8(lrb_engine * e, const unsigned char * frames, int n_frames, int width, int height, int channels,
+                               long long pitch, long long frame_stride, float min_length,
+                               lrb_frame_info * info, lrb_segment * lines, int lines_cap);
+LRB_API int lrb_detect_device_u8(lrb_engine * e, const unsigned char * frames, int n_frames, int width, int height, int channels,
+                                 long long pitch, long long frame_stride, float min_length,
+                                 lrb_frame_info * info, lrb_segment * lines, int lines_cap);
+LRB_API int lrb_rectify_host_u8(lrb_engine * e, const unsigned char * frames, int n_frames, int width, int height, int channels,
+                                long long pitch, long long frame_stride, float min_length,
+                                const lrb_config * cfg, int n_cfg, lrb_transform * transforms, lrb_frame_info * info);
+LRB_API int lrb_rectify_device_u8(lrb_engine * e, const unsigned char * frames, int n_frames, int width, int height, int channels,
+                                  long long pitch, long long frame_stride, float min_length,
+                                  const lrb_config * cfg, int n_cfg, lrb_transform * transforms, lrb_frame_info * info);
+
 /* detect + compute_rectification_transform per frame (the whole hot path); cfg is one config for all frames
  * (n_cfg == 1) or one per frame cycled modulo n_cfg.  transforms: host array [n_frames]. */
 LRB_API int lrb_rectify_device(lrb_engine * e, const float * frames, int n_frames, int width, int height,

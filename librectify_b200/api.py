@@ -59,6 +59,10 @@ def load_library(path: str | None = None):
     lib.lrb_version.restype = C.c_char_p
     lib.lrb_set_seed.argtypes = [C.c_uint]; lib.lrb_set_seed.restype = None
     lib.lrb_engine_set_refine.argtypes = [vp, ip]
+    for name in ("lrb_detect_host_u8", "lrb_detect_device_u8"):
+        getattr(lib, name).argtypes = [vp, vp, ip, ip, ip, ip, ll, ll, fp, vp, vp, ip]
+    for name in ("lrb_rectify_host_u8", "lrb_rectify_device_u8"):
+        getattr(lib, name).argtypes = [vp, vp, ip, ip, ip, ip, ll, ll, fp, vp, ip, vp, vp]
     lib.lrb_engine_create.argtypes = [ip, ip, C.POINTER(vp)]
     lib.lrb_engine_destroy.argtypes = [vp]; lib.lrb_engine_destroy.restype = None
     lib.lrb_engine_slots.argtypes = [vp]
@@ -239,6 +243,44 @@ class Engine:
         tf = np.zeros(n, TF_DTYPE)
         fn = self.lib.lrb_rectify_device if dev else self.lib.lrb_rectify_host
         self._check(fn(self.h, ptr, n, w, h, pitch, fs, C.c_float(min_length), cfg.ctypes.data, len(cfg), tf.ctypes.data, info.ctypes.data))
+        self.w, self.h_ = w, h
+        return tf, info
+
+    # 8-bit frames (gray [n,h,w] or BGR [n,h,w,3]; numpy = host, torch CUDA tensor = device) ----------------------------
+    @staticmethod
+    def _frames_args_u8(frames):
+        if isinstance(frames, np.ndarray):
+            a = frames
+            if a.ndim == 2 or (a.ndim == 3 and a.shape[-1] == 3 and a.strides[-1] == 1 and a.strides[-2] == 3):
+                a = a[None]
+            ch = 3 if a.ndim == 4 else 1
+            assert a.dtype == np.uint8 and a.strides[-1] == 1 and (ch == 1 or a.strides[2] == 3)
+            fs = a.strides[0] if a.shape[0] > 1 else a.shape[1] * a.strides[1]
+            return a.ctypes.data, a.shape[0], a.shape[1], a.shape[2], ch, a.strides[1], fs, False, a
+        import torch
+        t = frames
+        ch = 3 if t.dim() == 4 else 1
+        assert t.dtype == torch.uint8 and t.is_contiguous() and t.dim() in (3, 4)
+        return t.data_ptr(), t.shape[0], t.shape[1], t.shape[2], ch, t.stride(1), t.stride(0), t.is_cuda, t
+
+    def detect_u8(self, frames, min_length: float, lines_cap: int = 4096):
+        ptr, n, h, w, ch, pitch, fs, dev, keep = self._frames_args_u8(frames)
+        info = np.zeros(n, INFO_DTYPE)
+        lines = np.zeros((n, lines_cap), SEG_DTYPE)
+        fn = self.lib.lrb_detect_device_u8 if dev else self.lib.lrb_detect_host_u8
+        self._check(fn(self.h, ptr, n, w, h, ch, pitch, fs, C.c_float(min_length), info.ctypes.data, lines.ctypes.data, lines_cap))
+        self.w, self.h_ = w, h
+        if int(info["n_lines"].max(initial=0)) > lines_cap:
+            return self.detect_u8(frames, min_length, int(info["n_lines"].max()))
+        return info, [lines[i, :info["n_lines"][i]].copy() for i in range(n)]
+
+    def rectify_u8(self, frames, min_length: float, cfg: np.ndarray | None = None):
+        ptr, n, h, w, ch, pitch, fs, dev, keep = self._frames_args_u8(frames)
+        cfg = make_config() if cfg is None else np.ascontiguousarray(cfg, CFG_DTYPE)
+        info = np.zeros(n, INFO_DTYPE)
+        tf = np.zeros(n, TF_DTYPE)
+        fn = self.lib.lrb_rectify_device_u8 if dev else self.lib.lrb_rectify_host_u8
+        self._check(fn(self.h, ptr, n, w, h, ch, pitch, fs, C.c_float(min_length), cfg.ctypes.data, len(cfg), tf.ctypes.data, info.ctypes.data))
         self.w, self.h_ = w, h
         return tf, info
 

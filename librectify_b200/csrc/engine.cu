@@ -88,6 +88,7 @@ struct lrb_engine {
     // host input: the next group's frames are copied on a second stream as soon as K1 of the current group has consumed
     // the image workspace, so the copy overlaps flood / fit / RANSAC of the current group
     cudaStream_t st_copy = nullptr; cudaEvent_t ev_k1_done = nullptr, ev_copy_done = nullptr; bool pre_copied = false;
+    unsigned char * u8_stage = nullptr; size_t u8_stage_bytes = 0;    // device staging of 8-bit host frames (lrb_*_host_u8)
     // workspace geometry
     int w = 0, h = 0, pitch = 0;
     size_t plane = 0;                  // elements per slot plane
@@ -258,8 +259,19 @@ void collect_profile(lrb_engine * e, const std::vector<int> & order)
     }
 }
 
+// 8-bit input (u8.channels != 0): `frames` is ignored, pitch / fstride are in bytes
+struct U8Src { const unsigned char * data = nullptr; int channels = 0; bool on_device = false; };
+
 int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w, int h, long long pitch,
-              long long fstride, float min_length, int n_next);
+              long long fstride, float min_length, int n_next, U8Src u8);
+
+int copy_host_u8(lrb_engine * e, const unsigned char * src, int n, int w, int h, int ch, long long pitch, long long fstride, cudaStream_t st)
+{
+    const size_t row = (size_t)w * ch;
+    for (int i = 0; i < n; ++i)
+        CK(cudaMemcpy2DAsync(e->u8_stage + (size_t)i * row * h, row, src + (long long)i * fstride, (size_t)pitch, row, h, cudaMemcpyHostToDevice, st));
+    return 0;
+}
 
 void copy_host_frames(lrb_engine * e, const float * frames, int n, int w, int h, long long pitch, long long fstride, cudaStream_t st)
 {
@@ -273,7 +285,7 @@ void copy_host_frames(lrb_engine * e, const float * frames, int n, int w, int h,
 
 // n_next > 0: the n_next frames that follow this group in the caller's host buffer form the next group (host input only)
 int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w, int h, long long pitch,
-              long long fstride, float min_length, int n_next)
+              long long fstride, float min_length, int n_next, U8Src u8)
 {
     if (n < 1 || n > e->slots) return fail(-1, "group of %d frames does not fit %d slots", n, e->slots);
     CK(cudaSetDevice(e->device));
@@ -305,7 +317,32 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     CK(cudaMemsetAsync(e->P.vis - ((size_t)kMarginY * e->pitch + kMarginX), 0, e->plane * n, e->st));
     CUtensorMap tm_user; const CUtensorMap * tm = &e->tm_img;
     Planes P1 = e->P; int tma_x = kMarginX, tma_y = kMarginY;      // K1's view: where the input image lives
-    if (on_device) {
+    if (u8.channels) {
+        // 8-bit frames: (host: staged on the device first) -> gray / 256 into the image workspace
+        const size_t row = (size_t)w * u8.channels, need = row * h * e->slots;
+        const unsigned char * dsrc = u8.data; long long dpitch = pitch, dstride = fstride;
+        if (!u8.on_device) {
+            if (e->u8_stage_bytes < need) {
+                CK(cudaStreamSynchronize(e->st)); CK(cudaStreamSynchronize(e->st_copy));
+                if (e->u8_stage) CK(cudaFree(e->u8_stage));
+                e->u8_stage = nullptr; e->u8_stage_bytes = 0;
+                CK(cudaMalloc(&e->u8_stage, need)); e->u8_stage_bytes = need;
+                e->pre_copied = false;
+            }
+            if (e->pre_copied) { CK(cudaStreamWaitEvent(e->st, e->ev_copy_done, 0)); e->pre_copied = false; }
+            else if (int r = copy_host_u8(e, u8.data, n, w, h, u8.channels, pitch, fstride, e->st)) return r;
+            dsrc = e->u8_stage; dpitch = (long long)row; dstride = (long long)(row * h);
+        }
+        launch_ingest_u8(dsrc, dpitch, dstride, u8.channels, e->ws_img, e->pitch, e->plane, w, h, n, e->st); e->kernels++;
+        static const bool no_prefetch_u8 = getenv("LRB_NO_PREFETCH") != nullptr;
+        if (!u8.on_device && n_next > 0 && !no_prefetch_u8) {             // the staging buffer is free again after the ingest kernel
+            CK(cudaEventRecord(e->ev_k1_done, e->st));
+            CK(cudaStreamWaitEvent(e->st_copy, e->ev_k1_done, 0));
+            if (int r = copy_host_u8(e, u8.data + (long long)n * fstride, n_next, w, h, u8.channels, pitch, fstride, e->st_copy)) return r;
+            CK(cudaEventRecord(e->ev_copy_done, e->st_copy));
+            e->pre_copied = true;
+        }
+    } else if (on_device) {
         const bool direct = pitch > 0 && (reinterpret_cast<uintptr_t>(frames) % 16 == 0) && (pitch % 4 == 0) &&
                             (n == 1 || (fstride > 0 && fstride % 4 == 0));
         if (direct) {
@@ -329,7 +366,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     stage(LRB_T_GRAD);
     launch_grad(*tm, P1, e->ctrl, n, tma_x, tma_y, e->st);
     static const bool no_prefetch = getenv("LRB_NO_PREFETCH") != nullptr;
-    if (!on_device && n_next > 0 && !no_prefetch) {                       // the image workspace is free again after K1
+    if (!on_device && !u8.channels && n_next > 0 && !no_prefetch) {       // the image workspace is free again after K1
         CK(cudaEventRecord(e->ev_k1_done, e->st));
         CK(cudaStreamWaitEvent(e->st_copy, e->ev_k1_done, 0));
         copy_host_frames(e, frames + (long long)n * fstride, n_next, w, h, pitch, fstride, e->st_copy);
@@ -374,7 +411,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
                 if (e->seed_div > 1) {                    // plateau-like input: every pixel can be a peak; enlarge the seed arrays once
                     e->seed_div = 1;
                     if (e->pre_copied) { CK(cudaStreamSynchronize(e->st_copy)); e->pre_copied = false; }   // the workspace is rebuilt: copy again
-                    return run_group(e, frames, on_device, n, w, h, pitch, fstride, min_length, n_next);
+                    return run_group(e, frames, on_device, n, w, h, pitch, fstride, min_length, n_next, u8);
                 }
                 return fail(-4, "frame %d: more than %d gradient peaks (seed capacity)", i, e->S.cap);
             }
@@ -423,16 +460,19 @@ void fill_info(const lrb_engine * e, int i, lrb_frame_info * out)
 
 int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, int w, int h, long long pitch,
            long long fstride, float min_length, lrb_frame_info * info, lrb_segment * lines, int lines_cap,
-           const lrb_config * cfg, int n_cfg, lrb_transform * tf)
+           const lrb_config * cfg, int n_cfg, lrb_transform * tf, U8Src u8 = U8Src())
 {
     if (!e) return fail(-1, "null engine");
-    if (n_frames < 0 || !frames) return fail(-1, "bad arguments");
+    if (n_frames < 0 || (!frames && !u8.channels)) return fail(-1, "bad arguments");
+    if (u8.channels && (!u8.data || (u8.channels != 1 && u8.channels != 3) || pitch < (long long)w * u8.channels))
+        return fail(-1, "8-bit input: 1 (gray) or 3 (BGR) channels, pitch in bytes >= width * channels");
     if (pitch < 0 && n_frames != 1) return fail(-1, "negative pitch is only supported for a single frame");
     std::vector<lrb_segment> tmp;
     for (int f0 = 0; f0 < n_frames; f0 += e->slots) {
         const int n = std::min(e->slots, n_frames - f0);
         const int n_next = std::min(e->slots, n_frames - f0 - n);
-        if (int r = run_group(e, frames + (long long)f0 * fstride, on_device, n, w, h, pitch, fstride, min_length, n_next)) {
+        U8Src g8 = u8; if (u8.channels) g8.data = u8.data + (long long)f0 * fstride;
+        if (int r = run_group(e, u8.channels ? nullptr : frames + (long long)f0 * fstride, on_device, n, w, h, pitch, fstride, min_length, n_next, g8)) {
             if (e->pre_copied) { cudaStreamSynchronize(e->st_copy); e->pre_copied = false; }
             return r;
         }

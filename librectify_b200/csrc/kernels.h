@@ -41,6 +41,8 @@ void launch_mt_stream(unsigned seed, unsigned * stream, unsigned long long n, cu
 // ingest.cu
 void launch_ingest(const float * src, long long src_pitch, long long src_frame_stride, float * dst, int dst_pitch,
                    size_t dst_stride, int w, int h, int n_slots, cudaStream_t st);
+void launch_ingest_u8(const unsigned char * src, long long src_pitch, long long src_frame_stride, int channels, float * dst,
+                      int dst_pitch, size_t dst_stride, int w, int h, int n_slots, cudaStream_t st);
 void launch_fill_u32(unsigned * p, size_t n, unsigned v, cudaStream_t st);
 
 } // namespace lrb

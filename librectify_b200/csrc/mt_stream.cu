@@ -75,7 +75,36 @@ __global__ void k_ingest(const float * __restrict__ src, long long src_pitch, lo
     for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < w; x += gridDim.x * blockDim.x) d[x] = s[x];
 }
 
+// 8-bit ingest (what the reference's demo does on the CPU before calling the library):
+//   channels == 1: gray / 256                      cv::Mat::convertTo(CV_32F, 1/256.0), reference src/autorectify.cpp:119
+//   channels == 3: BGR -> gray first, OpenCV's 8-bit fixed point (b*3735 + g*19235 + r*9798 + 2^14) >> 15
+//                  (cv::cvtColor COLOR_BGR2GRAY as the demo calls it; pinned against cv2 in tests/golden/ingest_u8.npz)
+// x / 256 is exact in float, so the result is bit-identical to the float frame the CPU path would have passed.
+template <int CH>
+__global__ void k_ingest_u8(const unsigned char * __restrict__ src, long long src_pitch, long long src_frame_stride,
+                            float * __restrict__ dst, int dst_pitch, size_t dst_stride, int w, int h)
+{
+    const int slot = blockIdx.z;
+    const int y = blockIdx.y;
+    const unsigned char * s = src + (long long)slot * src_frame_stride + (long long)y * src_pitch;
+    float * d = dst + slot * dst_stride + (size_t)y * dst_pitch;
+    for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < w; x += gridDim.x * blockDim.x) {
+        unsigned g;
+        if (CH == 1) g = s[x];
+        else g = ((unsigned)s[3 * x] * 3735u + (unsigned)s[3 * x + 1] * 19235u + (unsigned)s[3 * x + 2] * 9798u + (1u << 14)) >> 15;
+        d[x] = __fmul_rn((float)g, 0.00390625f);
+    }
+}
+
 } // namespace
+
+void launch_ingest_u8(const unsigned char * src, long long src_pitch, long long src_frame_stride, int channels, float * dst,
+                      int dst_pitch, size_t dst_stride, int w, int h, int n_slots, cudaStream_t st)
+{
+    dim3 grid((w + 255) / 256, h, n_slots);
+    if (channels == 1) k_ingest_u8<1><<<grid, 256, 0, st>>>(src, src_pitch, src_frame_stride, dst, dst_pitch, dst_stride, w, h);
+    else               k_ingest_u8<3><<<grid, 256, 0, st>>>(src, src_pitch, src_frame_stride, dst, dst_pitch, dst_stride, w, h);
+}
 
 void launch_mt_stream(unsigned seed, unsigned * stream, unsigned long long n, cudaStream_t st)
 {

@@ -46,7 +46,7 @@ class Runner:
             tot["groups"] += p["groups"]; tot["kernels"] += p["kernels"]
         return tot
 
-    def rectify(self, frames, min_length: float, cfg=None):
+    def rectify(self, frames, min_length: float, cfg=None, u8: bool = False):
         """frames: [n, h, w] numpy (host) or torch CUDA tensor.  Returns (transforms[n], info[n])."""
         n = frames.shape[0]
         k = len(self.engines)
@@ -58,7 +58,8 @@ class Runner:
             if hi <= lo:
                 return
             try:
-                t, i = self.engines[j].rectify(frames[lo:hi], min_length, cfg)
+                eng = self.engines[j]
+                t, i = (eng.rectify_u8 if u8 else eng.rectify)(frames[lo:hi], min_length, cfg)
                 tf[lo:hi] = t; info[lo:hi] = i
             except Exception as ex:  # surfaced to the caller below
                 errs.append(ex)

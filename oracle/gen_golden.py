@@ -90,10 +90,24 @@ def refine_case(ref: Ref) -> dict:
                 lines_plain=ref.find_line_segment_groups(img, 5.0, refine=False, num_threads=-1, seed=0))
 
 
+def ingest_case(ref: Ref) -> dict:
+    """8-bit ingest: a BGR crop of the bundled photo, OpenCV's BGR2GRAY of it (cv2, this container), and the
+    reference's result on gray/256 — what src/autorectify.cpp:119,340 feed the library"""
+    import cv2
+    bgr = cv2.imread("/root/reference/doc/image.jpg")[100:420, 200:680].copy()
+    gray = cv2.cvtColor(bgr, cv2.COLOR_BGR2GRAY)
+    img = gray.astype(np.float32) / np.float32(256.0)
+    return dict(bgr=bgr, gray=gray, min_length=np.float32(5.0),
+                lines=ref.find_line_segment_groups(img, 5.0, refine=False, num_threads=-1, seed=0))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = Ref("canon")
     from librectify_b200.synth import manhattan_frame
+    if "--ingest-only" in sys.argv:
+        np.savez_compressed(os.path.join(GOLD, "ingest_u8.npz"), **ingest_case(ref))
+        return
     if "--refine-only" in sys.argv:                       # added after the other fixtures were committed: leave those untouched
         np.savez_compressed(os.path.join(GOLD, "refine.npz"), **refine_case(ref))
         return
@@ -143,6 +157,7 @@ def main():
         case["gray_u8"] = g
         np.savez_compressed(os.path.join(GOLD, "doc_image.npz"), **case)
     np.savez_compressed(os.path.join(GOLD, "refine.npz"), **refine_case(ref))
+    np.savez_compressed(os.path.join(GOLD, "ingest_u8.npz"), **ingest_case(ref))
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 
