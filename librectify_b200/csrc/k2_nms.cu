@@ -24,7 +24,7 @@ namespace lrb {
 
 namespace {
 
-constexpr int K2_TW = 128, K2_TH = 32;
+constexpr int K2_TW = 128, K2_TH = 32, K2_RPT = 8, K2_THREADS = 32 * (K2_TH / K2_RPT);
 // TMA box origins must be 16-byte aligned along x: the mag tile starts 4 floats, the bin tile 16 bytes left of the tile
 constexpr int K2_MW = 4 + K2_TW + 4, K2_MH = K2_TH + 4;    // mag tile: columns x0-4 .. x0+131, rows y0-2 .. y0+33
 constexpr int K2_BW = 160, K2_BH = K2_TH + 2;              // bin tile: columns x0-16 .. x0+143, rows y0-1 .. y0+32
@@ -38,19 +38,32 @@ __device__ __forceinline__ int seed_bucket(float mag, float thr, float gmax)
     return kSeedBuckets - 1 - b;
 }
 
-__global__ void __launch_bounds__(256)
+// same bucket with the scale factor hoisted (identical arithmetic)
+__device__ __forceinline__ int seed_bucket_scaled(float mag, float thr, float scale)
+{
+    int b = (int)__fmul_rn(__fsub_rn(mag, thr), scale);
+    b = min(max(b, 0), kSeedBuckets - 1);
+    return kSeedBuckets - 1 - b;
+}
+
+__device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }   // one FMNMX3
+
+// 4 warps per CTA; a thread owns 4 columns x 8 rows of the 128 x 32 tile.  Instruction budget per pixel (SASS): ~2 shared
+// loads, ~4 three-input maxima, 2 for the peak decision, ~4 for the packed-byte dilation.
+__global__ void __launch_bounds__(K2_THREADS)
 k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
                Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y)
 {
     __shared__ __align__(128) float tmag[K2_MH * K2_MW];
     __shared__ __align__(128) uint8_t tbin[K2_BH * K2_BW];
     __shared__ __align__(8) uint64_t bar;
+    __shared__ int s_cnt, s_base;
 
     const int slot = blockIdx.z;
     const int x0 = blockIdx.x * K2_TW, y0 = blockIdx.y * K2_TH;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); s_cnt = 0; }
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_arrive_expect_tx(&bar, K2_MH * K2_MW * 4 + K2_BH * K2_BW);
@@ -59,96 +72,105 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
     }
     const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
     const float thr = __fmul_rn(gmax, kSeedFactor);
+    // mag >= 0 and thr >= 0: for a finite float m, m > thr <=> m >= tup, tup = the float after thr
+    const float tup = __uint_as_float(__float_as_uint(thr) + 1u);
+    const int ty0 = warp * K2_RPT;              // K2_RPT output rows per thread
+    const int xq = x0 + lane * 4;               // 4 output columns per thread
     mbar_wait(&bar, 0);
 
-    const int ty0 = warp * 4;                   // 4 output rows per thread
-    const int xq = x0 + lane * 4;               // 4 output columns per thread
-
     // ---- 5x5 maximum, separable (max is exact and order-free) ----------------------------------------------------
-    float hm[8][4], ctr[4][4];
+    // A peak needs mag == window max and mag > thr; tup is folded into the window max, so the test is one equality.
+    // The 2-px image border and everything outside the image have mag == 0 (K1 writes the reference's zero border, TMA
+    // zero-fills), and 0 < tup, so no position test is needed.
+    float hm[K2_RPT + 4][4];
+    float4 ctr[K2_RPT];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const float4 q0 = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4]);
-        const float4 q1 = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4 + 4]);
-        const float4 q2 = *reinterpret_cast<const float4 *>(&tmag[(ty0 + i) * K2_MW + lane * 4 + 8]);
-        const float p[8] = {q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y};      // image columns xq-2 .. xq+5
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            hm[i][c] = fmaxf(fmaxf(fmaxf(p[c], p[c + 1]), fmaxf(p[c + 2], p[c + 3])), p[c + 4]);
-            if (i >= 2 && i < 6) ctr[i - 2][c] = p[c + 2];
-        }
+    for (int i = 0; i < K2_RPT + 4; ++i) {
+        const float * row = &tmag[(ty0 + i) * K2_MW + lane * 4];
+        const float4 q0 = *reinterpret_cast<const float4 *>(row);
+        const float4 q1 = *reinterpret_cast<const float4 *>(row + 4);
+        const float4 q2 = *reinterpret_cast<const float4 *>(row + 8);
+        // image columns xq-2 .. xq+5 = q0.z q0.w q1.x q1.y q1.z q1.w q2.x q2.y
+        const float core = fmax3(q1.x, q1.y, q1.z);
+        hm[i][0] = fmax3(core, q0.z, q0.w);
+        hm[i][1] = fmax3(core, q0.w, q1.w);
+        hm[i][2] = fmax3(core, q1.w, q2.x);
+        hm[i][3] = fmax3(fmax3(q1.y, q1.z, q1.w), q2.x, q2.y);
+        if (i >= 2 && i < K2_RPT + 2) ctr[i - 2] = q1;
     }
     unsigned peakmask = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int y = y0 + ty0 + j;
-        const bool vy = (y >= 2) && (y < P.h - 2);
+    for (int c = 0; c < 4; ++c) {
+        float pr[K2_RPT / 2 + 2];               // pr[k] = max(rows 2k, 2k+1, tup)
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float mx = fmaxf(fmaxf(fmaxf(hm[j][c], hm[j + 1][c]), fmaxf(hm[j + 2][c], hm[j + 3][c])), hm[j + 4][c]);
-            const int x = xq + c;
-            const bool v = vy && (x >= 2) && (x < P.w - 2);
-            if (v && ctr[j][c] == mx && ctr[j][c] > thr) peakmask |= 1u << (j * 4 + c);
+        for (int k = 0; k < K2_RPT / 2 + 2; ++k) pr[k] = fmax3(hm[2 * k][c], hm[2 * k + 1][c], tup);
+#pragma unroll
+        for (int k = 0; k < K2_RPT / 2; ++k) {
+            const float ve = fmax3(pr[k], pr[k + 1], hm[2 * k + 4][c]);          // rows 2k   .. 2k+4
+            const float vo = fmax3(hm[2 * k + 1][c], pr[k + 1], pr[k + 2]);      // rows 2k+1 .. 2k+5
+            const float ce = c == 0 ? ctr[2 * k].x : c == 1 ? ctr[2 * k].y : c == 2 ? ctr[2 * k].z : ctr[2 * k].w;
+            const float co = c == 0 ? ctr[2 * k + 1].x : c == 1 ? ctr[2 * k + 1].y : c == 2 ? ctr[2 * k + 1].z : ctr[2 * k + 1].w;
+            if (ce == ve) peakmask |= 1u << ((2 * k) * 4 + c);
+            if (co == vo) peakmask |= 1u << ((2 * k + 1) * 4 + c);
         }
     }
 
-    // ---- 3x3 dilation of the one-hot bin masks ---------------------------------------------------------------------
+    // ---- 3x3 dilation of the one-hot bin masks, four pixels per word -------------------------------------------------
     // tbin row i <-> image row y0-1+i, byte k <-> image column x0-16+k; this thread needs columns xq-1 .. xq+4 = bytes 4*lane+15 .. +20
-    unsigned hor[6];                            // per staged row: 4 bytes, byte c = OR of one-hot(bin) over columns c-1..c+1
+    unsigned hor[K2_RPT + 2];                   // per staged row: byte c = OR of one-hot(bin) over columns xq+c-1 .. xq+c+1
 #pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        const unsigned w0 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 12]);
-        const unsigned w1 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 16]);
-        const unsigned w2 = *reinterpret_cast<const unsigned *>(&tbin[(ty0 + i) * K2_BW + lane * 4 + 20]);
-        unsigned oh[6];
-        oh[0] = 1u << ((w0 >> 24) & 7u);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) oh[k + 1] = 1u << ((w1 >> (8 * k)) & 7u);
-        oh[5] = 1u << (w2 & 7u);
+    for (int i = 0; i < K2_RPT + 2; ++i) {
+        const uint8_t * row = &tbin[(ty0 + i) * K2_BW + lane * 4];
+        const unsigned w1 = *reinterpret_cast<const unsigned *>(row + 16);
+        const unsigned bl = row[15], br = row[20];
+        // one-hot of the four bytes by a byte-table lookup: selector nibble c = bin of byte c
+        const unsigned t = w1 | (w1 >> 4);
+        const unsigned oh = __byte_perm(0x08040201u, 0x80402010u, __byte_perm(t, 0u, 0x4420u));
         // out-of-image staged bytes are 0 (bin 0); they are only ever combined into border pixels, which are forced to 0
-        hor[i] = (oh[0] | oh[1] | oh[2]) | ((oh[1] | oh[2] | oh[3]) << 8) | ((oh[2] | oh[3] | oh[4]) << 16) | ((oh[3] | oh[4] | oh[5]) << 24);
+        hor[i] = (oh | (oh << 8) | (oh >> 8)) | (1u << bl) | (0x01000000u << br);
     }
+    unsigned colkeep = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { const int x = xq + c; if (x >= 1 && x < P.w - 1) colkeep |= 0xFFu << (8 * c); }
     uint8_t * pmask = P.mask8 + slot * P.stride;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < K2_RPT; ++j) {
         const int y = y0 + ty0 + j;
         if (y < P.h && xq < P.wq) {
-            unsigned mword = hor[j] | hor[j + 1] | hor[j + 2];
+            const unsigned mword = hor[j] | hor[j + 1] | hor[j + 2];
             const bool vy = (y >= 1) && (y < P.h - 1);
-            unsigned keep = 0;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) { const int x = xq + c; if (vy && x >= 1 && x < P.w - 1) keep |= 0xFFu << (8 * c); }
-            *reinterpret_cast<unsigned *>(pmask + (size_t)y * P.pitch + xq) = mword & keep;
+            *reinterpret_cast<unsigned *>(pmask + (size_t)y * P.pitch + xq) = vy ? (mword & colkeep) : 0u;
         }
     }
 
-    // ---- append peaks: one atomic per warp --------------------------------------------------------------------------
+    // ---- append peaks: one global atomic per CTA (list order is irrelevant, K3 ranks exactly) ----------------------
     const int cnt = __popc(peakmask);
-    int incl = cnt;
-#pragma unroll
-    for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += t; }
-    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    int o = 0;
+    if (cnt) o = atomicAdd(&s_cnt, cnt);
+    __syncthreads();
+    const int total = s_cnt;
     if (total == 0) return;
-    int base = 0;
-    if (lane == 0) base = atomicAdd(&ctrl[slot].n_seeds, total);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    int o = base + incl - cnt;
+    if (threadIdx.x == 0) s_base = atomicAdd(&ctrl[slot].n_seeds, total);
+    __syncthreads();
+    if (!cnt) return;
+    o += s_base;
+    const float scale = __fdiv_rn((float)kSeedBuckets, __fsub_rn(gmax, thr));
     unsigned * us_mag = S.us_mag + (size_t)slot * S.cap; unsigned * us_idx = S.us_idx + (size_t)slot * S.cap;
     int * hist = S.hist + (size_t)slot * kSeedBuckets;
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-            if (peakmask & (1u << (j * 4 + c))) {
-                if (o < S.cap) {
-                    us_mag[o] = __float_as_uint(ctr[j][c]);
-                    us_idx[o] = (unsigned)((y0 + ty0 + j) * P.w + (xq + c));      // raster index in the dense W x H image
-                    atomicAdd(&hist[seed_bucket(ctr[j][c], thr, gmax)], 1);
-                } else {
-                    ctrl[slot].seed_overflow = 1;
-                }
-                ++o;
-            }
+    while (peakmask) {
+        const int b = __ffs(peakmask) - 1;
+        peakmask &= peakmask - 1;
+        const int j = b >> 2, c = b & 3;
+        if (o < S.cap) {
+            const float m = tmag[(ty0 + 2 + j) * K2_MW + lane * 4 + 4 + c];
+            us_mag[o] = __float_as_uint(m);
+            us_idx[o] = (unsigned)((y0 + ty0 + j) * P.w + (xq + c));      // raster index in the dense W x H image
+            atomicAdd(&hist[seed_bucket_scaled(m, thr, scale)], 1);
+        } else {
+            ctrl[slot].seed_overflow = 1;
+        }
+        ++o;
+    }
 }
 
 // exclusive scan of the bucket histogram; one block of 1024 threads per frame, 4 buckets per thread
@@ -257,7 +279,7 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
                 FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st)
 {
     dim3 grid((P.w + K2_TW - 1) / K2_TW, (P.h + K2_TH - 1) / K2_TH, n_slots);
-    k_nms5x5_seeds<<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    k_nms5x5_seeds<<<grid, K2_THREADS, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
 }
 
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st)
