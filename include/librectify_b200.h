@@ -99,6 +99,36 @@ LRB_API int lrb_rectify_device_u8(lrb_engine * e, const unsigned char * frames, 
                                   long long pitch, long long frame_stride, float min_length,
                                   const lrb_config * cfg, int n_cfg, lrb_transform * transforms, lrb_frame_info * info);
 
+/* ---- the demo's image operations either side of the hot path, on the device ------------------
+ * The reference delegates them to OpenCV; they are restated from OpenCV's published algorithms and pinned against cv2.
+ *
+ * prescale_image (reference src/autorectify.cpp:56-67): scale = min(float(max_size) / max(w, h), 1.0f) and
+ * cv::resize(INTER_AREA) to cvRound(w * scale) x cvRound(h * scale).  lrb_prescale_size reports the size and scale,
+ * lrb_prescale_area_f32 resizes one float frame (pitches in elements; *_on_device: the pointer is device memory). */
+LRB_API int lrb_prescale_size(int width, int height, int max_size, int * dst_width, int * dst_height, float * scale);
+LRB_API int lrb_prescale_area_f32(lrb_engine * e, const float * src, int src_on_device, int width, int height, long long pitch,
+                                  int max_size, float * dst, int dst_on_device, long long dst_pitch);
+/* homography_from_corners (reference src/autorectify.cpp:152-192): output size and the 3x3 homography (row-major
+ * double[9], h33 = 1) that maps the source corners onto the transform's corners; clip = 3.0 in the demo. */
+LRB_API int lrb_homography_from_corners(const lrb_transform * t, float clip, double * H9, int * dst_width, int * dst_height);
+/* cv::warpPerspective(src, dst, H, Size(dst_width, dst_height)) with INTER_LINEAR and a constant 0 border (reference
+ * src/autorectify.cpp:359) for 8-bit images of 1 or 3 channels; pitches in BYTES; inverse_map != 0: H9 maps
+ * destination to source (cv::WARP_INVERSE_MAP). */
+LRB_API int lrb_warp_perspective_u8(lrb_engine * e, const unsigned char * src, int src_on_device, int width, int height, int channels,
+                                    long long pitch, const double * H9, int inverse_map, unsigned char * dst, int dst_on_device,
+                                    int dst_width, int dst_height, long long dst_pitch);
+
+/* The whole flow of the reference's demo for one 8-bit image (reference src/autorectify.cpp:113-148,330-360): gray,
+ * /256, prescale to max_size (< 1: fraction of the larger side), find_line_segment_groups with min_length =
+ * max(w,h)/100 of the prescaled frame, lines scaled back, compute_rectification_transform for the original size,
+ * homography_from_corners(clip), warpPerspective of the input.  lines: host array [lines_cap] (truncated, *n_lines is
+ * the true count); warped: host buffer of warped_bytes (needs warped_width * warped_height * channels; -5 if too small,
+ * the size is reported either way).  All image work runs on the device. */
+LRB_API int lrb_autorectify_u8(lrb_engine * e, const unsigned char * image, int width, int height, int channels, long long pitch,
+                               float max_size, int refine, const lrb_config * cfg, float clip,
+                               lrb_transform * tf, lrb_segment * lines, int lines_cap, int * n_lines,
+                               unsigned char * warped, size_t warped_bytes, int * warped_width, int * warped_height);
+
 /* detect + compute_rectification_transform per frame (the whole hot path); cfg is one config for all frames
  * (n_cfg == 1) or one per frame cycled modulo n_cfg.  transforms: host array [n_frames]. */
 LRB_API int lrb_rectify_device(lrb_engine * e, const float * frames, int n_frames, int width, int height,

@@ -74,6 +74,11 @@ def load_library(path: str | None = None):
     lib.lrb_compute_transform_from_vp.argtypes = [ip, ip, vp, vp, vp]; lib.lrb_compute_transform_from_vp.restype = None
     lib.lrb_fit_vanishing_point.argtypes = [vp, ip, ip, vp]; lib.lrb_fit_vanishing_point.restype = None
     lib.lrb_assign_to_group.argtypes = [vp, ip, vp, ip, fp]; lib.lrb_assign_to_group.restype = None
+    lib.lrb_prescale_size.argtypes = [ip, ip, ip, C.POINTER(ip), C.POINTER(ip), C.POINTER(fp)]
+    lib.lrb_prescale_area_f32.argtypes = [vp, vp, ip, ip, ip, ll, ip, vp, ip, ll]
+    lib.lrb_homography_from_corners.argtypes = [vp, fp, vp, C.POINTER(ip), C.POINTER(ip)]
+    lib.lrb_warp_perspective_u8.argtypes = [vp, vp, ip, ip, ip, ip, ll, vp, ip, vp, ip, ip, ip, ll]
+    lib.lrb_autorectify_u8.argtypes = [vp, vp, ip, ip, ip, ll, fp, ip, vp, fp, vp, vp, ip, C.POINTER(ip), vp, C.c_size_t, C.POINTER(ip), C.POINTER(ip)]
     lib.lrb_stage_fetch.argtypes = [vp, ip, ip, vp, C.c_size_t]; lib.lrb_stage_fetch.restype = ll
     lib.lrb_profile_enable.argtypes = [vp, ip]; lib.lrb_profile_enable.restype = None
     lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None
@@ -283,6 +288,58 @@ class Engine:
         self._check(fn(self.h, ptr, n, w, h, ch, pitch, fs, C.c_float(min_length), cfg.ctypes.data, len(cfg), tf.ctypes.data, info.ctypes.data))
         self.w, self.h_ = w, h
         return tf, info
+
+    # the demo's image operations either side of the path (reference src/autorectify.cpp) ---------------
+    def prescale(self, image: np.ndarray, max_size: int):
+        """prescale_image (src/autorectify.cpp:56-67): cv::resize(INTER_AREA) of a float frame; returns (frame, scale)."""
+        a = np.ascontiguousarray(image, np.float32)
+        h, w = a.shape
+        dw, dh, sc = C.c_int(), C.c_int(), C.c_float()
+        self._check(self.lib.lrb_prescale_size(w, h, int(max_size), C.byref(dw), C.byref(dh), C.byref(sc)))
+        out = np.empty((dh.value, dw.value), np.float32)
+        self._check(self.lib.lrb_prescale_area_f32(self.h, a.ctypes.data, 0, w, h, w, int(max_size), out.ctypes.data, 0, dw.value))
+        return out, np.float32(sc.value)
+
+    def homography_from_corners(self, tf, clip: float = 3.0):
+        """homography_from_corners (src/autorectify.cpp:152-192): (H 3x3 float64, (dst_width, dst_height))."""
+        t = np.ascontiguousarray(tf, TF_DTYPE).reshape(-1)[:1]
+        H = np.zeros(9, np.float64)
+        dw, dh = C.c_int(), C.c_int()
+        self._check(self.lib.lrb_homography_from_corners(t.ctypes.data, C.c_float(clip), H.ctypes.data, C.byref(dw), C.byref(dh)))
+        return H.reshape(3, 3), (dw.value, dh.value)
+
+    def warp_perspective(self, image: np.ndarray, H: np.ndarray, dsize, inverse_map: bool = False) -> np.ndarray:
+        """cv::warpPerspective(image, H, dsize) (INTER_LINEAR, constant 0 border) of an 8-bit gray or BGR image on the device."""
+        a = np.ascontiguousarray(image, np.uint8)
+        ch = 1 if a.ndim == 2 else a.shape[2]
+        h, w = a.shape[:2]
+        dw, dh = int(dsize[0]), int(dsize[1])
+        Hc = np.ascontiguousarray(H, np.float64).reshape(9)
+        out = np.empty((dh, dw) if a.ndim == 2 else (dh, dw, ch), np.uint8)
+        self._check(self.lib.lrb_warp_perspective_u8(self.h, a.ctypes.data, 0, w, h, ch, w * ch, Hc.ctypes.data, 1 if inverse_map else 0,
+                                                     out.ctypes.data, 0, dw, dh, dw * ch))
+        return out
+
+    def autorectify(self, image: np.ndarray, max_size: float = 1200, refine: bool = False, cfg: np.ndarray | None = None, clip: float = 3.0):
+        """The flow of the reference's demo for one 8-bit gray / BGR image (src/autorectify.cpp:113-148,330-360), all image
+        work on the device (lrb_autorectify_u8).  Returns (warped image or None, transform, lines)."""
+        a = np.ascontiguousarray(image, np.uint8)
+        ch = 1 if a.ndim == 2 else a.shape[2]
+        h, w = a.shape[:2]
+        cfg = make_config(horizontal_vp_min_distance=2.0) if cfg is None else np.ascontiguousarray(cfg, CFG_DTYPE)
+        tf = np.zeros(1, TF_DTYPE)
+        cap = 8192
+        lines = np.zeros(cap, SEG_DTYPE)
+        n, ww, wh = C.c_int(), C.c_int(), C.c_int()
+        buf = np.empty(int(w * clip) * int(h * clip) * ch + 16, np.uint8)
+        self._check(self.lib.lrb_autorectify_u8(self.h, a.ctypes.data, w, h, ch, w * ch, C.c_float(max_size), 1 if refine else 0,
+                                                cfg.ctypes.data, C.c_float(clip), tf.ctypes.data, lines.ctypes.data, cap, C.byref(n),
+                                                buf.ctypes.data, buf.size, C.byref(ww), C.byref(wh)))
+        warped = None
+        if ww.value > 0 and wh.value > 0:
+            shape = (wh.value, ww.value) if a.ndim == 2 else (wh.value, ww.value, ch)
+            warped = buf[: wh.value * ww.value * ch].reshape(shape).copy()
+        return warped, tf[0], lines[: min(n.value, cap)].copy()
 
     # stage window ------------------------------------------------------------------------------------------------------
     def fetch(self, stage: str, slot: int = 0, count: int | None = None) -> np.ndarray:

@@ -16,6 +16,7 @@
 // inside exact ties (std::sort is unstable there; the tests accept any order inside a tie group) — without a general
 // sort: bucket scan -> scatter -> exact rank inside the (tiny) bucket by counting.  The rank is the seed's flood
 // priority and its slot in every per-seed array.
+#include <cstdlib>
 #include "common.cuh"
 #include "tma.cuh"
 #include "kernels.h"
@@ -24,7 +25,7 @@ namespace lrb {
 
 namespace {
 
-constexpr int K2_TW = 128, K2_TH = 32, K2_RPT = 8, K2_THREADS = 32 * (K2_TH / K2_RPT);
+constexpr int K2_TW = 128, K2_TH = 32;
 // TMA box origins must be 16-byte aligned along x: the mag tile starts 4 floats, the bin tile 16 bytes left of the tile
 constexpr int K2_MW = 4 + K2_TW + 4, K2_MH = K2_TH + 4;    // mag tile: columns x0-4 .. x0+131, rows y0-2 .. y0+33
 constexpr int K2_BW = 160, K2_BH = K2_TH + 2;              // bin tile: columns x0-16 .. x0+143, rows y0-1 .. y0+32
@@ -50,7 +51,8 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf
 
 // 4 warps per CTA; a thread owns 4 columns x 8 rows of the 128 x 32 tile.  Instruction budget per pixel (SASS): ~2 shared
 // loads, ~4 three-input maxima, 2 for the peak decision, ~4 for the packed-byte dilation.
-__global__ void __launch_bounds__(K2_THREADS)
+template <int K2_RPT, int MINB>
+__global__ void __launch_bounds__(32 * (K2_TH / K2_RPT), MINB)
 k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
                Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y)
 {
@@ -279,7 +281,12 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
                 FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st)
 {
     dim3 grid((P.w + K2_TW - 1) / K2_TW, (P.h + K2_TH - 1) / K2_TH, n_slots);
-    k_nms5x5_seeds<<<grid, K2_THREADS, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    static const int cfg = [] { const char * v = getenv("LRB_K2_CFG"); return v ? atoi(v) : 2; }();
+    if (cfg == 1)      k_nms5x5_seeds<4, 4><<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    else if (cfg == 2) k_nms5x5_seeds<8, 6><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    else if (cfg == 3) k_nms5x5_seeds<4, 3><<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    else if (cfg == 4) k_nms5x5_seeds<8, 8><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    else               k_nms5x5_seeds<8, 5><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
 }
 
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st)

@@ -44,5 +44,14 @@ void launch_ingest(const float * src, long long src_pitch, long long src_frame_s
 void launch_ingest_u8(const unsigned char * src, long long src_pitch, long long src_frame_stride, int channels, float * dst,
                       int dst_pitch, size_t dst_stride, int w, int h, int n_slots, cudaStream_t st);
 void launch_fill_u32(unsigned * p, size_t n, unsigned v, cudaStream_t st);
+// k_warp.cu
+struct WarpMatrix { double m[9]; };    // destination -> source map, row-major (what cv::warpPerspective uses after inverting H)
+void launch_warp_perspective_u8(const unsigned char * src, int sw, int sh, long long spitch, int channels, unsigned char * dst, int dw, int dh,
+                                long long dpitch, const WarpMatrix & M, cudaStream_t st);
+void launch_resize_area_f32(const float * src, long long spitch, float * dst, int dw, int dh, long long dpitch,
+                            const int * xofs, const int * xsi, const float * xalpha, const int * yofs, const int * ysi, const float * yalpha,
+                            cudaStream_t st);
+void launch_resize_area_fast_f32(const float * src, int sw, int sh, long long spitch, float * dst, int dw, int dh, long long dpitch, int scale,
+                                 cudaStream_t st);
 
 } // namespace lrb
