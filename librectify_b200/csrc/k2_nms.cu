@@ -49,37 +49,15 @@ __device__ __forceinline__ int seed_bucket_scaled(float mag, float thr, float sc
 
 __device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }   // one FMNMX3
 
-// 4 warps per CTA; a thread owns 4 columns x 8 rows of the 128 x 32 tile.  Instruction budget per pixel (SASS): ~2 shared
-// loads, ~4 three-input maxima, 2 for the peak decision, ~4 for the packed-byte dilation.
-template <int K2_RPT, int MINB>
-__global__ void __launch_bounds__(32 * (K2_TH / K2_RPT), MINB)
-k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
-               Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y)
+// A thread owns 4 columns x K2_RPT rows of the 128 x 32 tile.  Instruction budget per pixel (SASS): ~2 shared loads,
+// ~4 three-input maxima, 2 for the peak decision, ~4 for the packed-byte dilation: ~24 in all.
+// One tile, staged in tmag / tbin: writes mask8, returns the peak bitmap of this thread (bit j*4+c = row j, column c).
+template <int K2_RPT>
+__device__ __forceinline__ unsigned nms_tile(const float * tmag, const uint8_t * tbin, const Planes & P, int slot, int x0, int y0, float tup,
+                                             int lane, int warp)
 {
-    __shared__ __align__(128) float tmag[K2_MH * K2_MW];
-    __shared__ __align__(128) uint8_t tbin[K2_BH * K2_BW];
-    __shared__ __align__(8) uint64_t bar;
-    __shared__ int s_cnt, s_base;
-
-    const int slot = blockIdx.z;
-    const int x0 = blockIdx.x * K2_TW, y0 = blockIdx.y * K2_TH;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); s_cnt = 0; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(&bar, K2_MH * K2_MW * 4 + K2_BH * K2_BW);
-        tma_load_3d(tmag, &tmap_mag, x0 - 4 + tma_x, y0 - 2 + tma_y, slot, &bar);
-        tma_load_3d(tbin, &tmap_bin, x0 - 16 + tma_x, y0 - 1 + tma_y, slot, &bar);
-    }
-    const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
-    const float thr = __fmul_rn(gmax, kSeedFactor);
-    // mag >= 0 and thr >= 0: for a finite float m, m > thr <=> m >= tup, tup = the float after thr
-    const float tup = __uint_as_float(__float_as_uint(thr) + 1u);
     const int ty0 = warp * K2_RPT;              // K2_RPT output rows per thread
     const int xq = x0 + lane * 4;               // 4 output columns per thread
-    mbar_wait(&bar, 0);
-
     // ---- 5x5 maximum, separable (max is exact and order-free) ----------------------------------------------------
     // A peak needs mag == window max and mag > thr; tup is folded into the window max, so the test is one equality.
     // The 2-px image border and everything outside the image have mag == 0 (K1 writes the reference's zero border, TMA
@@ -145,17 +123,26 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
         }
     }
 
-    // ---- append peaks: one global atomic per CTA (list order is irrelevant, K3 ranks exactly) ----------------------
+    return peakmask;
+}
+
+// Append this thread's peaks to the frame's (unordered) seed list: one global atomic per CTA (K3 ranks exactly, so the
+// list order is irrelevant).  *s_cnt must be 0 on entry; contains CTA barriers, so every thread of the CTA calls it.
+template <int K2_RPT>
+__device__ __forceinline__ void nms_append(unsigned peakmask, const float * tmag, int * s_cnt, int * s_base, const Planes & P, const Seeds & S,
+                                           FrameCtrl * ctrl, int slot, int x0, int y0, float gmax, float thr, int lane, int warp)
+{
+    const int ty0 = warp * K2_RPT, xq = x0 + lane * 4;
     const int cnt = __popc(peakmask);
     int o = 0;
-    if (cnt) o = atomicAdd(&s_cnt, cnt);
+    if (cnt) o = atomicAdd(s_cnt, cnt);
     __syncthreads();
-    const int total = s_cnt;
-    if (total == 0) return;
-    if (threadIdx.x == 0) s_base = atomicAdd(&ctrl[slot].n_seeds, total);
+    const int total = *s_cnt;
+    if (total == 0) return;                     // CTA-uniform
+    if (threadIdx.x == 0) *s_base = atomicAdd(&ctrl[slot].n_seeds, total);
     __syncthreads();
     if (!cnt) return;
-    o += s_base;
+    o += *s_base;
     const float scale = __fdiv_rn((float)kSeedBuckets, __fsub_rn(gmax, thr));
     unsigned * us_mag = S.us_mag + (size_t)slot * S.cap; unsigned * us_idx = S.us_idx + (size_t)slot * S.cap;
     int * hist = S.hist + (size_t)slot * kSeedBuckets;
@@ -172,6 +159,94 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
             ctrl[slot].seed_overflow = 1;
         }
         ++o;
+    }
+}
+
+// one tile per CTA
+template <int K2_RPT, int MINB>
+__global__ void __launch_bounds__(32 * (K2_TH / K2_RPT), MINB)
+k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
+               Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y)
+{
+    __shared__ __align__(128) float tmag[K2_MH * K2_MW];
+    __shared__ __align__(128) uint8_t tbin[K2_BH * K2_BW];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ int s_cnt, s_base;
+
+    const int slot = blockIdx.z;
+    const int x0 = blockIdx.x * K2_TW, y0 = blockIdx.y * K2_TH;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); s_cnt = 0; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(&bar, K2_MH * K2_MW * 4 + K2_BH * K2_BW);
+        tma_load_3d(tmag, &tmap_mag, x0 - 4 + tma_x, y0 - 2 + tma_y, slot, &bar);
+        tma_load_3d(tbin, &tmap_bin, x0 - 16 + tma_x, y0 - 1 + tma_y, slot, &bar);
+    }
+    const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
+    const float thr = __fmul_rn(gmax, kSeedFactor);
+    // mag >= 0 and thr >= 0: for a finite float m, m > thr <=> m >= tup, tup = the float after thr
+    const float tup = __uint_as_float(__float_as_uint(thr) + 1u);
+    mbar_wait(&bar, 0);
+    const unsigned peakmask = nms_tile<K2_RPT>(tmag, tbin, P, slot, x0, y0, tup, lane, warp);
+    nms_append<K2_RPT>(peakmask, tmag, &s_cnt, &s_base, P, S, ctrl, slot, x0, y0, gmax, thr, lane, warp);
+}
+
+// Persistent form (LRB_K2_CFG=10|11; NOT the default): a resident grid walks the tiles of all frames; while a tile is being evaluated the copy engine already
+// fetches the CTA's next one into the other stage (two mbarriers, phase = use count of the stage), so the HBM latency of
+// a tile hides behind the arithmetic of the previous one instead of idling the CTA (the one-shot form spends half of its
+// warp-cycles in the mbarrier wait: profiles/r1_k2_v2.md).  Measured on B200 (gpurun_out/sweep_k2.log): alone it is
+// faster (102 vs 123 us per 32 frames, 0.60 vs 0.49 of the HBM peak), but with four engines sharing the GPU the long-lived
+// CTAs delay the other engines' flood rounds and the whole job drops from 3290 to 2700 images/s - so the one-shot form stays
+// the default and this one is kept for single-engine use.
+constexpr int K2_BIN_BYTES = (K2_BH * K2_BW + 127) / 128 * 128;
+constexpr int K2_STAGE_OFF_BIN = 2 * K2_MH * K2_MW * 4;
+constexpr int K2_PERSIST_SMEM = K2_STAGE_OFF_BIN + 2 * K2_BIN_BYTES + 64 + 128;      // + barriers / counters + alignment slack
+static_assert((K2_MH * K2_MW * 4) % 128 == 0, "TMA destinations must stay 128-byte aligned");
+
+template <int K2_RPT, int MINB>
+__global__ void __launch_bounds__(32 * (K2_TH / K2_RPT), MINB)
+k_nms5x5_seeds_persistent(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
+                          Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y, int tiles_x, int tiles_y, int n_tiles)
+{
+    extern __shared__ unsigned char k2_smem_raw[];
+    unsigned char * sm = k2_smem_raw + ((128u - (smem_u32(k2_smem_raw) & 127u)) & 127u);
+    auto tmag_of = [&](int stage) { return reinterpret_cast<float *>(sm + stage * (K2_MH * K2_MW * 4)); };
+    auto tbin_of = [&](int stage) { return sm + K2_STAGE_OFF_BIN + stage * K2_BIN_BYTES; };
+    uint64_t * bar = reinterpret_cast<uint64_t *>(sm + K2_STAGE_OFF_BIN + 2 * K2_BIN_BYTES);          // bar[0], bar[1]
+    int * s_cnt = reinterpret_cast<int *>(bar + 2);                                                    // s_cnt[0], s_cnt[1]
+    int * s_base = s_cnt + 2;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int per_frame = tiles_x * tiles_y;
+    auto issue = [&](int t, int stage) {        // thread 0 only
+        const int slot = t / per_frame, r = t - slot * per_frame, by = r / tiles_x, bx = r - by * tiles_x;
+        mbar_arrive_expect_tx(&bar[stage], K2_MH * K2_MW * 4 + K2_BH * K2_BW);
+        tma_load_3d(tmag_of(stage), &tmap_mag, bx * K2_TW - 4 + tma_x, by * K2_TH - 2 + tma_y, slot, &bar[stage]);
+        tma_load_3d(tbin_of(stage), &tmap_bin, bx * K2_TW - 16 + tma_x, by * K2_TH - 1 + tma_y, slot, &bar[stage]);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init();
+        s_cnt[0] = 0; s_cnt[1] = 0;
+        if ((int)blockIdx.x < n_tiles) issue(blockIdx.x, 0);
+    }
+    __syncthreads();
+    int it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        const int stage = it & 1;
+        // stage^1 was last read in iteration it-1, which ended with a CTA barrier
+        if (threadIdx.x == 0) { if (t + (int)gridDim.x < n_tiles) issue(t + gridDim.x, stage ^ 1); s_cnt[stage ^ 1] = 0; }
+        const int slot = t / per_frame, r = t - slot * per_frame, by = r / tiles_x, bx = r - by * tiles_x;
+        const int x0 = bx * K2_TW, y0 = by * K2_TH;
+        const float gmax = __uint_as_float(__ldg(&ctrl[slot].gmax_bits));
+        const float thr = __fmul_rn(gmax, kSeedFactor);
+        const float tup = __uint_as_float(__float_as_uint(thr) + 1u);
+        mbar_wait(&bar[stage], (it >> 1) & 1);
+        const float * tm = tmag_of(stage);
+        const unsigned peakmask = nms_tile<K2_RPT>(tm, tbin_of(stage), P, slot, x0, y0, tup, lane, warp);
+        nms_append<K2_RPT>(peakmask, tm, &s_cnt[stage], s_base, P, S, ctrl, slot, x0, y0, gmax, thr, lane, warp);
+        __syncthreads();                        // everyone is done with this stage (and with s_base)
     }
 }
 
@@ -282,11 +357,25 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
 {
     dim3 grid((P.w + K2_TW - 1) / K2_TW, (P.h + K2_TH - 1) / K2_TH, n_slots);
     static const int cfg = [] { const char * v = getenv("LRB_K2_CFG"); return v ? atoi(v) : 2; }();
+    if (cfg >= 10) {                            // persistent, double-buffered
+        auto kern = (cfg == 11) ? k_nms5x5_seeds_persistent<8, 3> : (cfg == 12) ? k_nms5x5_seeds_persistent<4, 2> : k_nms5x5_seeds_persistent<8, 4>;
+        const int threads = (cfg == 12) ? 256 : 128;
+        static int per_sm = 0, n_sm = 148;
+        if (per_sm == 0) {
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_PERSIST_SMEM);
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, K2_PERSIST_SMEM) != cudaSuccess || per_sm < 1) per_sm = 1;
+            int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+        }
+        const int n_tiles = (int)(grid.x * grid.y * grid.z);
+        const int use_per_sm = (cfg == 13) ? 2 : (cfg == 14) ? 1 : per_sm;
+        const int blocks = n_tiles < n_sm * use_per_sm ? n_tiles : n_sm * use_per_sm;
+        kern<<<blocks, threads, K2_PERSIST_SMEM, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y, (int)grid.x, (int)grid.y, n_tiles);
+        return;
+    }
     if (cfg == 1)      k_nms5x5_seeds<4, 4><<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
-    else if (cfg == 2) k_nms5x5_seeds<8, 6><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
-    else if (cfg == 3) k_nms5x5_seeds<4, 3><<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
     else if (cfg == 4) k_nms5x5_seeds<8, 8><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
-    else               k_nms5x5_seeds<8, 5><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    else if (cfg == 0) k_nms5x5_seeds<8, 5><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    else               k_nms5x5_seeds<8, 6><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
 }
 
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st)
