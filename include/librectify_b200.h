@@ -147,6 +147,15 @@ LRB_API void lrb_fit_vanishing_point(const lrb_segment * lines, int n_lines, int
 LRB_API void lrb_assign_to_group(const lrb_segment * lines, int n_lines, lrb_segment * new_lines, int n_new_lines,
                                  float angular_tolerance_deg);
 
+/* ---- the reference's dormant Hough-voted estimator ---------------------------------------------
+ * LinePencilModel::get_weights (reference src/line_pencil.cpp:47-86: 20 000 pair intersections voted into a 65 x 65
+ * accumulator, weight = inclination^4 towards the winning cell's direction) and DirectEstimator::solve (reference
+ * src/estimator.h:82-96: fit_optimal over weights > 0.95) on the pencil model of `lines`, restricted to the observations
+ * idx[0..n_idx) (NULL = all).  weights: host float[n_idx] or NULL; cell2: winning accumulator cell (u, v) or NULL;
+ * vp3: the estimated vanishing point (unit vector, normalised coordinates) or NULL. */
+LRB_API int lrb_direct_estimate(lrb_engine * e, const lrb_segment * lines, int n_lines, const int * idx, int n_idx,
+                                float * weights, int * cell2, float * vp3);
+
 /* ---- stage window (parity tests): contents of slot `slot` after the last lrb_detect_* call on this engine --------- */
 enum lrb_stage {
     LRB_ST_DX = 0, LRB_ST_DY, LRB_ST_MAG,        /* float32 [h*w] */

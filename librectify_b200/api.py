@@ -79,6 +79,7 @@ def load_library(path: str | None = None):
     lib.lrb_homography_from_corners.argtypes = [vp, fp, vp, C.POINTER(ip), C.POINTER(ip)]
     lib.lrb_warp_perspective_u8.argtypes = [vp, vp, ip, ip, ip, ip, ll, vp, ip, vp, ip, ip, ip, ll]
     lib.lrb_autorectify_u8.argtypes = [vp, vp, ip, ip, ip, ll, fp, ip, vp, fp, vp, vp, ip, C.POINTER(ip), vp, C.c_size_t, C.POINTER(ip), C.POINTER(ip)]
+    lib.lrb_direct_estimate.argtypes = [vp, vp, ip, vp, ip, vp, vp, vp]
     lib.lrb_stage_fetch.argtypes = [vp, ip, ip, vp, C.c_size_t]; lib.lrb_stage_fetch.restype = ll
     lib.lrb_profile_enable.argtypes = [vp, ip]; lib.lrb_profile_enable.restype = None
     lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None
@@ -340,6 +341,17 @@ class Engine:
             shape = (wh.value, ww.value) if a.ndim == 2 else (wh.value, ww.value, ch)
             warped = buf[: wh.value * ww.value * ch].reshape(shape).copy()
         return warped, tf[0], lines[: min(n.value, cap)].copy()
+
+    def direct_estimate(self, lines: np.ndarray, idx: np.ndarray | None = None):
+        """The reference's Hough-voted DirectEstimator (src/line_pencil.cpp:47-86, src/estimator.h:82-96).
+        Returns (weights[len(idx)], (u, v) winning accumulator cell, vanishing point[3])."""
+        ln = np.ascontiguousarray(lines, SEG_DTYPE)
+        ix = None if idx is None else np.ascontiguousarray(idx, np.int32)
+        m = len(ln) if ix is None else len(ix)
+        w = np.zeros(m, np.float32); cell = np.zeros(2, np.int32); vp = np.zeros(3, np.float32)
+        self._check(self.lib.lrb_direct_estimate(self.h, ln.ctypes.data, len(ln), None if ix is None else ix.ctypes.data, m,
+                                                 w.ctypes.data, cell.ctypes.data, vp.ctypes.data))
+        return w, (int(cell[0]), int(cell[1])), vp
 
     # stage window ------------------------------------------------------------------------------------------------------
     def fetch(self, stage: str, slot: int = 0, count: int | None = None) -> np.ndarray:

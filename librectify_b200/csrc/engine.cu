@@ -88,7 +88,7 @@ struct lrb_engine {
     // host input: the next group's frames are copied on a second stream as soon as K1 of the current group has consumed
     // the image workspace, so the copy overlaps flood / fit / RANSAC of the current group
     cudaStream_t st_copy = nullptr; cudaEvent_t ev_k1_done = nullptr, ev_copy_done = nullptr; bool pre_copied = false;
-    void * aux[5] = {}; size_t aux_bytes[5] = {};   // device scratch of the warp / prescale / autorectify entry points (source, destination, tables, float frame, prescaled frame)
+    void * aux[7] = {}; size_t aux_bytes[7] = {};   // device scratch of the warp / prescale / autorectify entry points (source, destination, tables, float frame, prescaled frame, Hough work space, Hough generator outputs)
     unsigned char * u8_stage = nullptr; size_t u8_stage_bytes = 0;    // device staging of 8-bit host frames (lrb_*_host_u8)
     // workspace geometry
     int w = 0, h = 0, pitch = 0;

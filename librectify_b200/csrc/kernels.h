@@ -44,6 +44,14 @@ void launch_ingest(const float * src, long long src_pitch, long long src_frame_s
 void launch_ingest_u8(const unsigned char * src, long long src_pitch, long long src_frame_stride, int channels, float * dst,
                       int dst_pitch, size_t dst_stride, int w, int h, int n_slots, cudaStream_t st);
 void launch_fill_u32(unsigned * p, size_t n, unsigned v, cudaStream_t st);
+void launch_mt_raw(unsigned seed, unsigned * out, unsigned long long n, cudaStream_t st);
+// k_hough.cu
+size_t hough_out_bytes();
+int hough_draws();
+int hough_hypotheses();
+void launch_hough_direct(const float * seg7, int n_lines, const int * idx, int m, const unsigned * raw, int n_raw,
+                         float * h, float * anchor, float * dir, float * len, int * draws, int * hyp_cell, float * hyp_val,
+                         float * weights, int * inl, void * out, cudaStream_t st);
 // k_warp.cu
 struct WarpMatrix { double m[9]; };    // destination -> source map, row-major (what cv::warpPerspective uses after inverting H)
 void launch_warp_perspective_u8(const unsigned char * src, int sw, int sh, long long spitch, int channels, unsigned char * dst, int dw, int dh,

@@ -31,7 +31,7 @@ __device__ __forceinline__ unsigned canonical_k(unsigned raw)
     return (unsigned)k;
 }
 
-__global__ void __launch_bounds__(256) k_mt_stream(unsigned seed, unsigned * __restrict__ out, unsigned long long n)
+__global__ void __launch_bounds__(256) k_mt_stream(unsigned seed, unsigned * __restrict__ out, unsigned long long n, int raw)
 {
     __shared__ unsigned x[624];
     const int t = threadIdx.x;
@@ -41,19 +41,28 @@ __global__ void __launch_bounds__(256) k_mt_stream(unsigned seed, unsigned * __r
     }
     __syncthreads();
     for (unsigned long long base = 0; base < n; base += 624) {
+        // every phase reads all its operands, meets at a barrier and only then writes: element i's "next" operand
+        // x[i+1] belongs to the neighbouring thread (possibly of another warp) and must still hold its old value
         // phase 1: i in [0, 227): all operands old
-        if (t < 227) { const unsigned v = mt_twist(x[t], x[t + 1], x[t + 397]); __syncwarp(__activemask()); x[t] = v; }
+        unsigned v = 0;
+        if (t < 227) v = mt_twist(x[t], x[t + 1], x[t + 397]);
+        __syncthreads();
+        if (t < 227) x[t] = v;
         __syncthreads();
         // phase 2: i in [227, 454): far operand x[i-227] is new
-        if (t < 227) { const int i = 227 + t; const unsigned v = mt_twist(x[i], x[i + 1], x[i - 227]); x[i] = v; }
+        if (t < 227) { const int i = 227 + t; v = mt_twist(x[i], x[i + 1], x[i - 227]); }
+        __syncthreads();
+        if (t < 227) x[227 + t] = v;
         __syncthreads();
         // phase 3: i in [454, 624): far operand new; element 623 wraps to the new x[0]
-        if (t < 170) { const int i = 454 + t; const unsigned v = mt_twist(x[i], i == 623 ? x[0] : x[i + 1], x[i - 227]); x[i] = v; }
+        if (t < 170) { const int i = 454 + t; v = mt_twist(x[i], i == 623 ? x[0] : x[i + 1], x[i - 227]); }
+        __syncthreads();
+        if (t < 170) x[454 + t] = v;
         __syncthreads();
         for (int i = t; i < 624; i += 256) {
             unsigned y = x[i];
             y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
-            if (base + i < n) out[base + i] = canonical_k(y);
+            if (base + i < n) out[base + i] = raw ? y : canonical_k(y);
         }
         __syncthreads();
     }
@@ -108,7 +117,13 @@ void launch_ingest_u8(const unsigned char * src, long long src_pitch, long long 
 
 void launch_mt_stream(unsigned seed, unsigned * stream, unsigned long long n, cudaStream_t st)
 {
-    k_mt_stream<<<1, 256, 0, st>>>(seed, stream, n);
+    k_mt_stream<<<1, 256, 0, st>>>(seed, stream, n, 0);
+}
+
+// the generator's raw 32-bit outputs (std::mt19937::operator()), for std::uniform_int_distribution (k_hough.cu)
+void launch_mt_raw(unsigned seed, unsigned * out, unsigned long long n, cudaStream_t st)
+{
+    k_mt_stream<<<1, 256, 0, st>>>(seed, out, n, 1);
 }
 
 void launch_fill_u32(unsigned * p, size_t n, unsigned v, cudaStream_t st)

@@ -211,6 +211,18 @@ class _StageLib:
         self._f("fit_optimal")(C.c_void_p(segs.ctypes.data), C.c_int(len(segs)), _ip(idx), C.c_int(len(idx)), _fp(out))
         return out
 
+    def get_weights(self, segs, idx):
+        """LinePencilModel::get_weights (reference src/line_pencil.cpp:47-86): Hough-voted inclination^4 per listed segment"""
+        segs = np.ascontiguousarray(segs); idx = np.ascontiguousarray(idx, np.int32); out = np.zeros(len(idx), np.float32)
+        self._f("get_weights")(C.c_void_p(segs.ctypes.data), C.c_int(len(segs)), _ip(idx), C.c_int(len(idx)), _fp(out))
+        return out
+
+    def direct_solve(self, segs, idx):
+        """DirectEstimator::solve (reference src/estimator.h:82-96)"""
+        segs = np.ascontiguousarray(segs); idx = np.ascontiguousarray(idx, np.int32); out = np.zeros(3, np.float32)
+        self._f("direct_solve")(C.c_void_p(segs.ctypes.data), C.c_int(len(segs)), _ip(idx), C.c_int(len(idx)), _fp(out))
+        return out
+
     def choice_knuth(self, seed, n, count):
         pairs = np.zeros((count, 2), np.int32); nxt = C.c_uint(0)
         draws = self._f("choice_knuth")(C.c_uint(seed), C.c_int(n), C.c_int(count), _ip(pairs), C.byref(nxt))

@@ -101,9 +101,32 @@ def ingest_case(ref: Ref) -> dict:
                 lines=ref.find_line_segment_groups(img, 5.0, refine=False, num_threads=-1, seed=0))
 
 
+def hough_case(ref: Ref) -> dict:
+    """dormant estimator (SURVEY.md §8 f3): LinePencilModel::get_weights + DirectEstimator::solve of the compiled reference
+    (templates instantiated by oracle/ref_harness.cpp) on the segments of the committed fixtures"""
+    out = {}
+    names = []
+    for name in ("doc_image", "synth_320x240", "synth_640x360", "ingest_u8"):
+        g = np.load(os.path.join(GOLD, name + ".npz"))
+        segs = g["segs"] if "segs" in g.files else g["lines"]
+        n = len(segs)
+        lists = {"all": np.arange(n, dtype=np.int32), "third": np.arange(0, n, 3, dtype=np.int32),
+                 "rest": np.nonzero(segs["group_id"] != 0)[0].astype(np.int32), "few": np.array([5, 1, 9, 2], np.int32)}
+        for k, idx in lists.items():
+            tag = f"{name}:{k}"; names.append(tag)
+            out[tag + ":idx"] = idx
+            out[tag + ":weights"] = ref.get_weights(segs, idx)
+            out[tag + ":vp"] = ref.direct_solve(segs, idx)
+    out["cases"] = np.array(names)
+    return out
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = Ref("canon")
+    if "--hough-only" in sys.argv:                        # added after the other fixtures were committed: leave those untouched
+        np.savez_compressed(os.path.join(GOLD, "hough.npz"), **hough_case(ref))
+        return
     from librectify_b200.synth import manhattan_frame
     if "--ingest-only" in sys.argv:
         np.savez_compressed(os.path.join(GOLD, "ingest_u8.npz"), **ingest_case(ref))
@@ -158,6 +181,7 @@ def main():
         np.savez_compressed(os.path.join(GOLD, "doc_image.npz"), **case)
     np.savez_compressed(os.path.join(GOLD, "refine.npz"), **refine_case(ref))
     np.savez_compressed(os.path.join(GOLD, "ingest_u8.npz"), **ingest_case(ref))
+    np.savez_compressed(os.path.join(GOLD, "hough.npz"), **hough_case(ref))
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

@@ -561,6 +561,75 @@ void choice_knuth2(int N, MT19937 & rng, int out[2])
     }
 }
 
+/* ---- f3 (dormant in the reference): Hough-voted weights and the DirectEstimator ------------------------------------
+ * libstdc++ 13 uniform_int_distribution<int>(0, m-1) over mt19937 (bits/uniform_int_dist.h: 32-bit generator range ->
+ * Lemire's nearly divisionless method on a 64-bit product). */
+int uniform_int_below(MT19937 & rng, uint32_t m)
+{
+    uint64_t product = uint64_t(rng.next()) * uint64_t(m);
+    uint32_t low = uint32_t(product);
+    if (low < m) {
+        uint32_t threshold = uint32_t(-m) % m;
+        while (low < threshold) { product = uint64_t(rng.next()) * uint64_t(m); low = uint32_t(product); }
+    }
+    return int(product >> 32);
+}
+
+const int kHtSpace = 65, kHtHypotheses = 20000;      /* line_pencil.h:22-23 */
+
+/* LinePencilModel::get_weights, line_pencil.cpp:47-86; cell receives the winning accumulator cell (u, v) */
+void get_weights(const Model & M, const vector<int> & idx, vector<float> & w, int cell[2])
+{
+    const float k = std::floor(kHtSpace / 2.f), k1 = k - 1;
+    vector<float> acc(size_t(kHtSpace) * kHtSpace, 0.f);                 /* acc[u + 65 * v]: column-major like ArrayXXf */
+    MT19937 rng(5489u);                                                    /* std::mt19937() default seed */
+    const uint32_t m = uint32_t(idx.size());
+    for (int i = 0; i < kHtHypotheses; ++i) {
+        int a = idx[uniform_int_below(rng, m)];
+        int b = idx[uniform_int_below(rng, m)];
+        float x[3];
+        fit_pair(M, a, b, x);                                              /* h.row(a).cross(h.row(b)) */
+        if (std::fabs(x[0]) < 0.0001f && std::fabs(x[1]) < 0.0001f && std::fabs(x[2]) < 0.0001f) continue;
+        float z = sum3(x[0] * x[0], x[1] * x[1], x[2] * x[2]);             /* normalize(): z = squaredNorm; if (z > 0) x /= sqrt(z) */
+        if (z > 0.f) { float nr = std::sqrt(z); x[0] /= nr; x[1] /= nr; x[2] /= nr; }
+        if (x[2] < 0.f) { x[0] = -x[0]; x[1] = -x[1]; x[2] = -x[2]; }
+        int u = int(std::round(k1 * x[0] + k));
+        int v = int(std::round(k1 * x[1] + k));
+        acc[u + kHtSpace * v] += M.len[a] + M.len[b];
+    }
+    /* maxCoeff(&u, &v): Eigen's visitor walks a column-major array column by column and keeps the first strict maximum */
+    int mu = 0, mv = 0; float best = acc[0];
+    for (int v = 0; v < kHtSpace; ++v)
+        for (int u = 0; u < kHtSpace; ++u)
+            if (acc[u + kHtSpace * v] > best) { best = acc[u + kHtSpace * v]; mu = u; mv = v; }
+    cell[0] = mu; cell[1] = mv;
+    float p[3] = {(mu - k) / k1, (mv - k) / k1, 0.f};
+    float nrm = std::sqrt(sum3(p[0] * p[0], p[1] * p[1], p[2] * p[2]));
+    if (nrm > 1.f) { p[0] /= nrm; p[1] /= nrm; p[2] /= nrm; }              /* p /= p.norm(): the norm is evaluated again, same value */
+    p[2] = std::sqrt(1.f - (std::pow(p[0], 2.f) + std::pow(p[1], 2.f)));
+    w.resize(idx.size());
+    for (size_t i = 0; i < idx.size(); ++i) {
+        /* inclination(), geometry.cpp:214-229 */
+        float vx, vy; const int q = idx[i];
+        if (std::fabs(p[2]) < kEps) { vx = p[0]; vy = p[1]; }
+        else { float px = p[0] / p[2], py = p[1] / p[2]; vx = (-M.anchor[2*q]) + px; vy = (-M.anchor[2*q+1]) + py; }
+        float zz = vx * vx + vy * vy;
+        if (zz > 0.f) { float nr = std::sqrt(zz); vx = vx / nr; vy = vy / nr; }
+        float c = std::fabs(vx * M.dir[2*q] + vy * M.dir[2*q+1]);
+        w[i] = float(std::pow(double(c), 4.0));                            /* ArrayXf::pow(int): std::pow(float, int) promotes to double */
+    }
+}
+
+/* DirectEstimator::solve, estimator.h:82-96: inliers = weights > 0.95f, then fit_optimal (empty list -> all lines) */
+void direct_solve(const Model & M, const vector<int> & idx, float out[3])
+{
+    vector<float> w; int cell[2];
+    get_weights(M, idx, w, cell);
+    vector<int> inl;
+    for (size_t i = 0; i < idx.size(); ++i) if (w[i] > 0.95f) inl.push_back(idx[i]);
+    fit_optimal(M, inl, out);
+}
+
 float cos_threshold(float deg) { return 1.0f - std::cos(deg / 180.f * float(M_PI)); }      /* line_pencil.cpp:143-146 */
 
 struct Trace { int T; int * samples; float * scores; int * n_obs; int * winner; float * best_h; float * refined; };
@@ -847,6 +916,20 @@ void orc_fit_optimal(const OrcLineSegment * lines, int n, const int * idx, int n
 {
     Model M; build_model(lines, n, M);
     fit_optimal(M, vector<int>(idx, idx + n_idx), out3);
+}
+
+void orc_get_weights(const OrcLineSegment * lines, int n, const int * idx, int n_idx, float * w_out)
+{
+    Model M; build_model(lines, n, M);
+    vector<float> w; int cell[2];
+    get_weights(M, vector<int>(idx, idx + n_idx), w, cell);
+    for (int i = 0; i < n_idx; ++i) w_out[i] = w[i];
+}
+
+void orc_direct_solve(const OrcLineSegment * lines, int n, const int * idx, int n_idx, float * out3)
+{
+    Model M; build_model(lines, n, M);
+    direct_solve(M, vector<int>(idx, idx + n_idx), out3);
 }
 
 long long orc_choice_knuth(unsigned seed, int n, int count, int * pairs, unsigned * next_raw)

@@ -31,6 +31,7 @@
 #include "line_detector.h"
 #include "transform.h"
 #include "math_utils.h"
+#include "estimator.h"
 #include "threading.h"
 #include "utils.h"
 
@@ -192,6 +193,34 @@ void ref_fit_optimal(const LineSegment * lines, int n, const int * idx, int n_id
     LinePencilModel model(normalize_lines(v, p, s));
     Eigen::ArrayXi indices = Eigen::Map<const Eigen::ArrayXi>(idx, n_idx);
     Eigen::Vector3f r = model.fit_optimal(indices);
+    out3[0] = r.x(); out3[1] = r.y(); out3[2] = r.z();
+}
+
+/* dormant estimator: LinePencilModel::get_weights — Hough vote of 20 000 pair intersections on a
+ * 65x65 accumulator, reference src/line_pencil.cpp:47-86 — and DirectEstimator::solve, reference src/estimator.h:82-96.
+ * The templates are instantiated here; the reference's own build never does. */
+void ref_get_weights(const LineSegment * lines, int n, const int * idx, int n_idx, float * w_out)
+{
+    std::vector<LineSegment> v(lines, lines + n);
+    auto bb = bounding_box(v);
+    Eigen::Vector2f p = bbox_center(bb);
+    float s = bbox_size(bb).maxCoeff();
+    LinePencilModel model(normalize_lines(v, p, s));
+    Eigen::ArrayXi indices = Eigen::Map<const Eigen::ArrayXi>(idx, n_idx);
+    Eigen::ArrayXf w = model.get_weights(indices);
+    for (int i = 0; i < n_idx; ++i) w_out[i] = w(i);
+}
+
+void ref_direct_solve(const LineSegment * lines, int n, const int * idx, int n_idx, float * out3)
+{
+    std::vector<LineSegment> v(lines, lines + n);
+    auto bb = bounding_box(v);
+    Eigen::Vector2f p = bbox_center(bb);
+    float s = bbox_size(bb).maxCoeff();
+    LinePencilModel model(normalize_lines(v, p, s));
+    Eigen::ArrayXi indices = Eigen::Map<const Eigen::ArrayXi>(idx, n_idx);
+    DirectEstimator<LinePencilModel> est;
+    Eigen::Vector3f r = est.solve(model, indices, 0.f);
     out3[0] = r.x(); out3[1] = r.y(); out3[2] = r.z();
 }
 
