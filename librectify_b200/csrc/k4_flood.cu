@@ -416,6 +416,28 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     }
 }
 
+// Seeds of the coming window whose pixel already lies in a committed region are skipped by the sequential algorithm
+// (line_detector.cpp:103).  The flood kernel finds that out only after it has evaluated the seed's whole tile (the visited
+// byte arrives with the tile); from the second round on 40 % of the window seeds are in that state (ncu, profiles/), so
+// they are dropped here first, one byte load each.  Exact for the same reason as the -2 path of flood_tiles: the visited
+// mask only holds committed regions, and those belong to seeds of higher priority.
+__global__ void __launch_bounds__(256)
+k_flood_prune(Planes P, Seeds S, FrameCtrl * ctrl, int round, int slot0)
+{
+    const int slot = slot0 + blockIdx.y;
+    FrameCtrl & C = ctrl[slot];
+    if (C.live[round] == 0 || C.flood_overflow) return;
+    const int lo = C.win_lo, hi = C.win_hi;
+    const size_t so = (size_t)slot * S.cap;
+    const uint8_t * vis = P.vis + (size_t)slot * P.stride;
+    for (int rank = lo + blockIdx.x * blockDim.x + threadIdx.x; rank < hi; rank += gridDim.x * blockDim.x) {
+        if (S.status[so + rank] != kStatusLive) continue;
+        const unsigned spx = S.idx[so + rank];
+        const int sr = spx / P.w, sc = spx - sr * P.w;
+        if (vis[(size_t)sr * P.pitch + sc]) S.status[so + rank] = kStatusDropped;
+    }
+}
+
 // verify + commit + mark visited, one warp per window seed; the last block to finish moves the window
 __global__ void __launch_bounds__(256)
 k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first, int slot0)
@@ -570,7 +592,10 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
         const int ns = min(sub, n_slots - s0);
         const int fblocks = max(1, min((seeds_hint + FL_WARPS - 1) / FL_WARPS, (n_sm * per_sm + ns - 1) / ns));
         dim3 gf(fblocks, ns), gv(148 / max(1, min(ns, 4)) + 1, ns);
+        static const bool prune = getenv("LRB_FLOOD_NO_PRUNE") == nullptr;
+        dim3 gp(max(1, min((seeds_hint + 255) / 256, 64)), ns);
         for (int r = round_begin; r < round_end; ++r) {
+            if (prune && r > 0) { k_flood_prune<<<gp, 256, 0, st>>>(P, S, ctrl, r, s0); ++launches; }
             kern<<<gf, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
             k_flood_verify<<<gv, 256, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
             launches += 2;
