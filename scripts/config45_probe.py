@@ -1,0 +1,46 @@
+"""BASELINE configs 4 and 5 on one B200: parity against the oracle and timing.
+  config 4: 3840x2160 dense clutter, min_length 8 (N filtered ~ 2x10^4: stresses sampler + scoring)
+  config 5: 4000x3000 frames, rotate-only / mixed strategies cycled per frame"""
+import os, sys, time
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from librectify_b200 import api
+from librectify_b200.synth import manhattan_frame
+from oracle.bind import Oracle
+orc = Oracle()
+L = int(sys.argv[1]) if len(sys.argv) > 1 else 400
+img = manhattan_frame(3, 3840, 2160, n_lines=L, device="cuda")
+eng = api.Engine(0, 1)
+info, lines = eng.detect(img[None], 8.0, lines_cap=32768)
+torch.cuda.synchronize(); t0 = time.perf_counter()
+info, lines = eng.detect(img[None], 8.0, lines_cap=32768)
+torch.cuda.synchronize(); dt = time.perf_counter() - t0
+print("config4 L", L, "n_lines", int(info["n_lines"][0]), "raw", int(info["n_components"][0]), "seeds", int(info["n_seeds"][0]), "n_obs", info["n_obs"][0].tolist(),
+      "rounds", int(info["flood_rounds"][0]), "fallback", int(info["flood_fallback"][0]), "gpu ms", round(1e3 * dt, 1), flush=True)
+t0 = time.perf_counter()
+ref = orc.find_line_segment_groups(img.cpu().numpy(), 8.0, seed=0)
+print("oracle s", round(time.perf_counter() - t0, 1), "n", len(ref), "identical", lines[0].tobytes() == ref.tobytes(), flush=True)
+eng.close()
+if lines[0].tobytes() != ref.tobytes():
+    from tests.util import seeds_equal_modulo_ties, n_value_ties
+    a, b = lines[0], ref
+    geo = [f for f in api.SEG_DTYPE.names if f != "group_id"]
+    dg = np.nonzero(np.array([a[i][geo].tobytes() != b[i][geo].tobytes() for i in range(len(a))]))[0]
+    print("geometry diffs", len(dg), dg[:10], "group diffs", int((a["group_id"] != b["group_id"]).sum()))
+    for i in dg[:4]:
+        print("  gpu", a[i], "orc", b[i])
+    st = orc.detect_stages(img.cpu().numpy(), want_grad8=False)
+    eng = api.Engine(0, 1)
+    info, lines = eng.detect(img[None], 8.0, lines_cap=40000)
+    seeds = eng.fetch("seeds")
+    print("seeds identical", np.array_equal(seeds, st["seeds"]), "equal modulo ties", seeds_equal_modulo_ties(seeds, st["seeds"], st["mag"]), "ties", n_value_ties(st["seeds"], st["mag"]))
+    rs = eng.fetch("raw_segs"); cs = eng.fetch("comp_sizes")
+    print("raw count", len(rs), len(st["segs"]), "raw identical", rs.tobytes() == st["segs"].tobytes())
+    ka = np.lexsort((rs["y1"], rs["x1"])); kb = np.lexsort((st["segs"]["y1"], st["segs"]["x1"]))
+    same = rs[ka].tobytes() == st["segs"][kb].tobytes()
+    print("raw multiset identical", same)
+    if not same and len(rs) == len(st["segs"]):
+        d = np.nonzero(np.array([rs[ka][i].tobytes() != st["segs"][kb][i].tobytes() for i in range(len(rs))]))[0]
+        print("raw diffs", len(d)); 
+        for i in d[:4]: print("  ", rs[ka][i], st["segs"][kb][i], cs[ka][i], st["comp_sizes"][kb][i])
