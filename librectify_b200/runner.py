@@ -46,8 +46,13 @@ class Runner:
             tot["groups"] += p["groups"]; tot["kernels"] += p["kernels"]
         return tot
 
-    def rectify(self, frames, min_length: float, cfg=None, u8: bool = False):
-        """frames: [n, h, w] numpy (host) or torch CUDA tensor.  Returns (transforms[n], info[n])."""
+    def rectify(self, frames, min_length: float, cfg=None, u8: bool = False, steps: int = 1):
+        """frames: [n, h, w] numpy (host) or torch CUDA tensor.  Returns (transforms[n], info[n]).
+
+        steps > 1 streams the same batch through ``steps`` times (a benchmark's K steps, or K batches of a video): every
+        engine thread goes through its shard of each step — input copy, kernels, read-back, corner solve — and moves on to
+        the next step without waiting for the other engines, so one engine's host->device copy overlaps the others'
+        kernels instead of all engines copying at the start of every step.  The results of the last step are returned."""
         n = frames.shape[0]
         k = len(self.engines)
         tf = np.zeros(n, api.TF_DTYPE); info = np.zeros(n, api.INFO_DTYPE)
@@ -59,7 +64,8 @@ class Runner:
                 return
             try:
                 eng = self.engines[j]
-                t, i = (eng.rectify_u8 if u8 else eng.rectify)(frames[lo:hi], min_length, cfg)
+                for _ in range(max(1, steps)):
+                    t, i = (eng.rectify_u8 if u8 else eng.rectify)(frames[lo:hi], min_length, cfg)
                 tf[lo:hi] = t; info[lo:hi] = i
             except Exception as ex:  # surfaced to the caller below
                 errs.append(ex)
