@@ -8,6 +8,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdlib>
 
 namespace lrb {
 
@@ -161,6 +162,18 @@ __device__ __forceinline__ unsigned owner_epoch(unsigned o) { return o >> 24; }
 __device__ __forceinline__ unsigned owner_rank(unsigned o)  { return o & 0x00FFFFFFu; }
 
 struct SegRec { float x1, y1, x2, y2, weight, err; int group_id; };
+
+// Experiment knob: LRB_CARVEOUT = preferred shared-memory split (percent) for every hot kernel of the library; unset: the
+// driver's per-kernel choice.  Kernels of different engines share the SMs, and an SM keeps the largest split any resident
+// kernel asked for: LRB_CARVEOUT=100 (28 KB of L1 left) costs the flood 17 % (3415 -> 2830 images/s), 30..65 change nothing.
+// This is why no kernel of this library may ask for the maximum split (see launch_nms).
+inline int set_carveout(const void * kern)
+{
+    static const int pct = [] { const char * v = getenv("LRB_CARVEOUT"); return v ? atoi(v) : -1; }();
+    if (pct >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    return 0;
+}
+#define LRB_CARVEOUT(kern) do { static const int once_ = ::lrb::set_carveout(reinterpret_cast<const void *>(kern)); (void)once_; } while (0)
 
 // warp helpers
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

@@ -298,7 +298,7 @@ void launch_grad(const CUtensorMap & tmap, const Planes & P, FrameCtrl * ctrl, i
     if (cfg == 0)      k_grad5x5_bin<8, 8, 2><<<grid, 256, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
     else if (cfg == 2) k_grad5x5_bin<16, 4, 5><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
     else if (cfg == 3) k_grad5x5_bin<16, 4, 6><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
-    else               k_grad5x5_bin<16, 4, 4><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
+    else             { LRB_CARVEOUT((k_grad5x5_bin<16, 4, 4>)); k_grad5x5_bin<16, 4, 4><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y); }
 }
 
 int grad_tile_w() { return K1_SW; }

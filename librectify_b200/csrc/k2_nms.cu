@@ -193,13 +193,13 @@ k_nms5x5_seeds(const __grid_constant__ CUtensorMap tmap_mag, const __grid_consta
     nms_append<K2_RPT>(peakmask, tmag, &s_cnt, &s_base, P, S, ctrl, slot, x0, y0, gmax, thr, lane, warp);
 }
 
-// Persistent form (LRB_K2_CFG=10|11; NOT the default): a resident grid walks the tiles of all frames; while a tile is being evaluated the copy engine already
+// Persistent form (the default, LRB_K2_CFG=15: three CTAs per SM under a 150 KB shared-memory split): a resident grid walks the tiles of all frames; while a tile is being evaluated the copy engine already
 // fetches the CTA's next one into the other stage (two mbarriers, phase = use count of the stage), so the HBM latency of
 // a tile hides behind the arithmetic of the previous one instead of idling the CTA (the one-shot form spends half of its
-// warp-cycles in the mbarrier wait: profiles/r1_k2_v2.md).  Measured on B200 (gpurun_out/sweep_k2.log): alone it is
-// faster (102 vs 123 us per 32 frames, 0.60 vs 0.49 of the HBM peak), but with four engines sharing the GPU the long-lived
-// CTAs delay the other engines' flood rounds and the whole job drops from 3290 to 2700 images/s - so the one-shot form stays
-// the default and this one is kept for single-engine use.
+// warp-cycles in the mbarrier wait: profiles/r1_k2_v2.md).  Measured on B200 (profiles/r1_k2_forms.txt): 111 vs 124 us
+// per 32 frames (0.55 vs 0.49 of the HBM peak).  It must NOT be launched with the maximum shared-memory split (4 CTAs x 50 KB per
+// SM): the SMs then keep a 28 KB L1 and the other engines' flood kernels, which share them, lose a fifth of their speed
+// (whole job 3400 -> 2700 images/s) - hence the explicit 66 % preferred carveout in launch_nms.
 constexpr int K2_BIN_BYTES = (K2_BH * K2_BW + 127) / 128 * 128;
 constexpr int K2_STAGE_OFF_BIN = 2 * K2_MH * K2_MW * 4;
 constexpr int K2_PERSIST_SMEM = K2_STAGE_OFF_BIN + 2 * K2_BIN_BYTES + 64 + 128;      // + barriers / counters + alignment slack
@@ -247,6 +247,48 @@ k_nms5x5_seeds_persistent(const __grid_constant__ CUtensorMap tmap_mag, const __
         const unsigned peakmask = nms_tile<K2_RPT>(tm, tbin_of(stage), P, slot, x0, y0, tup, lane, warp);
         nms_append<K2_RPT>(peakmask, tm, &s_cnt[stage], s_base, P, S, ctrl, slot, x0, y0, gmax, thr, lane, warp);
         __syncthreads();                        // everyone is done with this stage (and with s_base)
+    }
+}
+
+// Two vertically adjacent tiles per CTA (LRB_K2_CFG=20): both tiles' boxes are issued at once, so the second tile's HBM
+// latency hides behind the first tile's arithmetic, while the CTA stays short-lived (the persistent form's long-lived CTAs are
+// what costs job throughput when several engines share the GPU).
+template <int K2_RPT, int MINB>
+__global__ void __launch_bounds__(32 * (K2_TH / K2_RPT), MINB)
+k_nms5x5_seeds_pair(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
+                    Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y, int tiles_y)
+{
+    extern __shared__ unsigned char k2_smem_raw[];
+    unsigned char * sm = k2_smem_raw + ((128u - (smem_u32(k2_smem_raw) & 127u)) & 127u);
+    uint64_t * bar = reinterpret_cast<uint64_t *>(sm + K2_STAGE_OFF_BIN + 2 * K2_BIN_BYTES);
+    int * s_cnt = reinterpret_cast<int *>(bar + 2);
+    int * s_base = s_cnt + 2;
+    const int slot = blockIdx.z;
+    const int x0 = blockIdx.x * K2_TW;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_mine = min(2, tiles_y - 2 * (int)blockIdx.y);
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init();
+        s_cnt[0] = 0; s_cnt[1] = 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 0; k < n_mine; ++k) {
+            const int y0 = (2 * blockIdx.y + k) * K2_TH;
+            mbar_arrive_expect_tx(&bar[k], K2_MH * K2_MW * 4 + K2_BH * K2_BW);
+            tma_load_3d(sm + k * (K2_MH * K2_MW * 4), &tmap_mag, x0 - 4 + tma_x, y0 - 2 + tma_y, slot, &bar[k]);
+            tma_load_3d(sm + K2_STAGE_OFF_BIN + k * K2_BIN_BYTES, &tmap_bin, x0 - 16 + tma_x, y0 - 1 + tma_y, slot, &bar[k]);
+        }
+    }
+    const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
+    const float thr = __fmul_rn(gmax, kSeedFactor);
+    const float tup = __uint_as_float(__float_as_uint(thr) + 1u);
+    for (int k = 0; k < n_mine; ++k) {
+        const int y0 = (2 * blockIdx.y + k) * K2_TH;
+        const float * tm = reinterpret_cast<const float *>(sm + k * (K2_MH * K2_MW * 4));
+        mbar_wait(&bar[k], 0);
+        const unsigned peakmask = nms_tile<K2_RPT>(tm, sm + K2_STAGE_OFF_BIN + k * K2_BIN_BYTES, P, slot, x0, y0, tup, lane, warp);
+        nms_append<K2_RPT>(peakmask, tm, &s_cnt[k], s_base, P, S, ctrl, slot, x0, y0, gmax, thr, lane, warp);
     }
 }
 
@@ -356,30 +398,48 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
                 FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st)
 {
     dim3 grid((P.w + K2_TW - 1) / K2_TW, (P.h + K2_TH - 1) / K2_TH, n_slots);
-    static const int cfg = [] { const char * v = getenv("LRB_K2_CFG"); return v ? atoi(v) : 2; }();
+    static const int cfg = [] { const char * v = getenv("LRB_K2_CFG"); return v ? atoi(v) : 15; }();
+    if (cfg >= 20) {                            // two tiles per CTA
+        auto kern = (cfg >= 21) ? k_nms5x5_seeds_pair<8, 3> : k_nms5x5_seeds_pair<8, 4>;
+        static bool once = false;
+        if (!once) {
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_PERSIST_SMEM);
+            // three CTAs per SM under a 164 KB split: a kernel that asks for the maximum split leaves the SMs with a 28 KB L1,
+            // and the other engines' flood kernels, which share those SMs, lose a fifth of their speed
+            if (cfg == 22) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
+            once = true;
+        }
+        dim3 g2(grid.x, (grid.y + 1) / 2, grid.z);
+        LRB_CARVEOUT(kern);
+        kern<<<g2, 128, K2_PERSIST_SMEM, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y, (int)grid.y);
+        return;
+    }
     if (cfg >= 10) {                            // persistent, double-buffered
-        auto kern = (cfg == 11) ? k_nms5x5_seeds_persistent<8, 3> : (cfg == 12) ? k_nms5x5_seeds_persistent<4, 2> : k_nms5x5_seeds_persistent<8, 4>;
+        auto kern = (cfg == 11 || cfg == 15) ? k_nms5x5_seeds_persistent<8, 3> : (cfg == 12) ? k_nms5x5_seeds_persistent<4, 2> : k_nms5x5_seeds_persistent<8, 4>;
         const int threads = (cfg == 12) ? 256 : 128;
         static int per_sm = 0, n_sm = 148;
         if (per_sm == 0) {
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_PERSIST_SMEM);
+            if (cfg == 15) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
             if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, K2_PERSIST_SMEM) != cudaSuccess || per_sm < 1) per_sm = 1;
             int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
         }
         const int n_tiles = (int)(grid.x * grid.y * grid.z);
-        const int use_per_sm = (cfg == 13) ? 2 : (cfg == 14) ? 1 : per_sm;
+        const int use_per_sm = (cfg == 13) ? 2 : (cfg == 14) ? 1 : (cfg == 15) ? 3 : per_sm;
         const int blocks = n_tiles < n_sm * use_per_sm ? n_tiles : n_sm * use_per_sm;
+        LRB_CARVEOUT(kern);
         kern<<<blocks, threads, K2_PERSIST_SMEM, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y, (int)grid.x, (int)grid.y, n_tiles);
         return;
     }
     if (cfg == 1)      k_nms5x5_seeds<4, 4><<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
     else if (cfg == 4) k_nms5x5_seeds<8, 8><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
     else if (cfg == 0) k_nms5x5_seeds<8, 5><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
-    else               k_nms5x5_seeds<8, 6><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
+    else             { LRB_CARVEOUT((k_nms5x5_seeds<8, 6>)); k_nms5x5_seeds<8, 6><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y); }
 }
 
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st)
 {
+    LRB_CARVEOUT(k_seed_scan); LRB_CARVEOUT(k_seed_scatter); LRB_CARVEOUT(k_seed_rank);
     k_seed_scan<<<n_slots, 1024, 0, st>>>(S, ctrl);
     dim3 grid((seeds_hint + 255) / 256, n_slots);
     k_seed_scatter<<<grid, 256, 0, st>>>(S, ctrl);

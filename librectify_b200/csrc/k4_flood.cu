@@ -594,6 +594,7 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
         dim3 gf(fblocks, ns), gv(148 / max(1, min(ns, 4)) + 1, ns);
         static const bool prune = getenv("LRB_FLOOD_NO_PRUNE") == nullptr;
         dim3 gp(max(1, min((seeds_hint + 255) / 256, 64)), ns);
+        LRB_CARVEOUT(kern); LRB_CARVEOUT(k_flood_verify); LRB_CARVEOUT(k_flood_prune);
         for (int r = round_begin; r < round_end; ++r) {
             if (prune && r > 0) { k_flood_prune<<<gp, 256, 0, st>>>(P, S, ctrl, r, s0); ++launches; }
             kern<<<gf, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);

@@ -297,6 +297,7 @@ __global__ void k_labels(Planes P, Comps K, FrameCtrl * ctrl, int * labels, int 
 
 void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int rounds_total, cudaStream_t st)
 {
+    LRB_CARVEOUT(k_comp_select); LRB_CARVEOUT(k_fit_segments);
     k_comp_select<<<n_slots, 1024, 0, st>>>(S, K, ctrl, rounds_total);
     dim3 grid(max(1, 148 * 8 / max(1, min(n_slots, 8))), n_slots);
     k_fit_segments<<<grid, FIT_WARPS * 32, 0, st>>>(P, S, K, ctrl);

@@ -299,6 +299,7 @@ __global__ void k_finalize(Lines L, FrameCtrl * ctrl)
 
 void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, bool refined, cudaStream_t st)
 {
+    LRB_CARVEOUT(k_filter_model); LRB_CARVEOUT(k_score); LRB_CARVEOUT(k_refit_assign); LRB_CARVEOUT(k_finalize);
     k_filter_model<<<n_slots, 1024, 0, st>>>(K, L, ctrl, min_length, rounds_total, refined ? refine_output(K, 0) : nullptr, (size_t)K.cap_pool);
 }
 

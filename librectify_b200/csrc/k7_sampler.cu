@@ -241,6 +241,7 @@ void launch_sampler(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsign
                     int solve, int T, cudaStream_t st)
 {
     dim3 g((kSampWorkers + 3) / 4, n_slots);
+    LRB_CARVEOUT(k_sampler_segments); LRB_CARVEOUT(k_sampler_link); LRB_CARVEOUT(k_sampler_stitch); LRB_CARVEOUT(k_sampler_tail);
     k_sampler_segments<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
     k_sampler_link<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
     k_sampler_stitch<<<n_slots, 256, 0, st>>>(L, ctrl, solve, T);
