@@ -287,6 +287,58 @@ k_grad5x5_bin(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ct
     }
 }
 
+// Persistent form: a resident grid walks the tiles of all frames with two TMA stages per CTA, so the next tile is in
+// flight while the current one is evaluated (the one-shot form spends 17 % of its stall samples in the mbarrier wait at CTA
+// start).  8 warps x 8 rows per 128 x 64 tile, two CTAs per SM: 2 x 2 x 37 KB of shared memory, inside the 66 % split that
+// keeps the L1 the flood kernels of the other engines need (see launch_nms in k2_nms.cu).
+template <int RPT, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB)
+k_grad5x5_bin_persistent(const __grid_constant__ CUtensorMap tmap, Planes P, FrameCtrl * ctrl, int tma_x, int tma_y,
+                         int tiles_x, int tiles_y, int n_tiles)
+{
+    constexpr int TH = WARPS * RPT, SH = TH + 4, STAGE = SH * K1_SW * (int)sizeof(float);
+    static_assert(STAGE % 128 == 0, "TMA destinations must stay 128-byte aligned");
+    extern __shared__ unsigned char k1_smem_raw[];
+    unsigned char * sm = k1_smem_raw + ((128u - (smem_u32(k1_smem_raw) & 127u)) & 127u);
+    uint64_t * bar = reinterpret_cast<uint64_t *>(sm + 2 * STAGE);
+    unsigned * wmax = reinterpret_cast<unsigned *>(bar + 2);                 // [2][WARPS]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int per_frame = tiles_x * tiles_y;
+    auto issue = [&](int t, int stage) {        // thread 0 only
+        const int slot = t / per_frame, r = t - slot * per_frame, by = r / tiles_x, bx = r - by * tiles_x;
+        mbar_arrive_expect_tx(&bar[stage], STAGE);
+        tma_load_3d(sm + stage * STAGE, &tmap, bx * K1_TW - K1_HALO_L + tma_x, by * TH - 2 + tma_y, slot, &bar[stage]);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init();
+        if ((int)blockIdx.x < n_tiles) issue(blockIdx.x, 0);
+    }
+    __syncthreads();
+    int it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        const int stage = it & 1;
+        if (threadIdx.x == 0 && t + (int)gridDim.x < n_tiles) issue(t + gridDim.x, stage ^ 1);   // stage^1 was released by the barrier that ended iteration it-1
+        const int slot = t / per_frame, r = t - slot * per_frame, by = r / tiles_x, bx = r - by * tiles_x;
+        const int x0 = bx * K1_TW, y0 = by * TH;
+        const float * tile = reinterpret_cast<const float *>(sm + stage * STAGE);
+        mbar_wait(&bar[stage], (it >> 1) & 1);
+        const bool interior = (x0 >= 2) && (x0 + K1_TW <= P.w - 2) && (y0 >= 2) && (y0 + TH <= P.h - 2);
+        const float tmax = interior ? compute_strip<RPT, true>(tile, P, slot, x0, y0, lane, warp)
+                                    : compute_strip<RPT, false>(tile, P, slot, x0, y0, lane, warp);
+        unsigned um = __float_as_uint(tmax);
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) um = max(um, __shfl_xor_sync(0xffffffffu, um, s));
+        if (lane == 0) wmax[stage * WARPS + warp] = um;
+        __syncthreads();                        // everyone is done with this stage; the warp maxima are complete
+        if (threadIdx.x == 0) {
+            unsigned v = wmax[stage * WARPS];
+#pragma unroll
+            for (int k = 1; k < WARPS; ++k) v = max(v, wmax[stage * WARPS + k]);
+            if (v) atomicMax(&ctrl[slot].gmax_bits, v);
+        }
+    }
+}
+
 } // namespace
 
 void launch_grad(const CUtensorMap & tmap, const Planes & P, FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st)
@@ -295,6 +347,20 @@ void launch_grad(const CUtensorMap & tmap, const Planes & P, FrameCtrl * ctrl, i
     // per thread; the taller strip amortises the 4-row halo (products of 20 input rows per 16 output rows instead of 12 per 8)
     static const int cfg = [] { const char * v = getenv("LRB_K1_CFG"); return v ? atoi(v) : 1; }();
     dim3 grid((P.w + K1_TW - 1) / K1_TW, (P.h + 63) / 64, n_slots);
+    if (cfg >= 10) {                            // persistent, double-buffered
+        auto kern = k_grad5x5_bin_persistent<8, 8, 2>;
+        constexpr int smem = 2 * (64 + 4) * K1_SW * (int)sizeof(float) + 64 + 8 * 8 + 128;
+        static int n_sm = 0;
+        if (n_sm == 0) {
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
+            int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+        }
+        const int n_tiles = (int)(grid.x * grid.y * grid.z);
+        const int blocks = n_tiles < 2 * n_sm ? n_tiles : 2 * n_sm;
+        kern<<<blocks, 256, smem, st>>>(tmap, P, ctrl, tma_x, tma_y, (int)grid.x, (int)grid.y, n_tiles);
+        return;
+    }
     if (cfg == 0)      k_grad5x5_bin<8, 8, 2><<<grid, 256, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
     else if (cfg == 2) k_grad5x5_bin<16, 4, 5><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
     else if (cfg == 3) k_grad5x5_bin<16, 4, 6><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
