@@ -3,7 +3,7 @@
   config 5: 4000x3000 frames, rotate-only / mixed strategies cycled per frame"""
 import os, sys, time
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from librectify_b200 import api
 from librectify_b200.synth import manhattan_frame

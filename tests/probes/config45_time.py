@@ -2,7 +2,7 @@
 frames, 4 engines x 4 slots), and the reference's OpenMP CPU path on the same frames (oracle/_ref/librectify_ship.so)."""
 import os, sys, time
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from librectify_b200 import api
 from librectify_b200.runner import Runner
