@@ -42,3 +42,24 @@ def test_homography_from_corners_against_cv2(golden):
         xs = c[:, 0]; ys = c[:, 1]
         xmin = (xs.max() + xs.min()) / 2 - 0.5 * min(xs.max() - xs.min(), 480 * 3.0)
         assert abs(p[0] / p[2] - (c[3, 0] - xmin)) < 1e-3
+
+
+def test_homography_degenerate_corners_are_rejected():
+    api, lib = _lib()
+    t = np.zeros(1, api.TF_DTYPE)
+    t["width"], t["height"] = 640, 480                               # all four corners at the origin: no homography exists
+    H = np.zeros(9); dw, dh = C.c_int(), C.c_int()
+    rc = lib.lrb_homography_from_corners(t.ctypes.data, C.c_float(3.0), H.ctypes.data, C.byref(dw), C.byref(dh))
+    assert rc != 0 and b"degenerate" in lib.lrb_last_error()
+    assert lib.lrb_homography_from_corners(None, C.c_float(3.0), H.ctypes.data, C.byref(dw), C.byref(dh)) != 0
+
+
+def test_identity_transform_gives_identity_homography():
+    api, lib = _lib()
+    t = np.zeros(1, api.TF_DTYPE)
+    t["width"], t["height"] = 640, 480
+    t["top_left"] = (0, 0, 1); t["top_right"] = (640, 0, 1); t["bottom_left"] = (0, 480, 1); t["bottom_right"] = (640, 480, 1)
+    H = np.zeros(9); dw, dh = C.c_int(), C.c_int()
+    assert lib.lrb_homography_from_corners(t.ctypes.data, C.c_float(3.0), H.ctypes.data, C.byref(dw), C.byref(dh)) == 0
+    assert (dw.value, dh.value) == (640, 480)
+    assert np.allclose(H.reshape(3, 3), np.eye(3), atol=1e-12)
