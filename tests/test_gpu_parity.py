@@ -296,3 +296,19 @@ def test_full_size_properties_4k(api, oracle):
     ref = oracle.find_line_segment_groups(img, 38.4, seed=0)
     assert lines[0].tobytes() == ref.tobytes()
     e.close()
+
+
+def test_runner_streamed_steps_match_single_step(api):
+    """Runner.rectify(steps=K) streams K passes of the batch through the engines without a join between them (bench.py's
+    timed region); the results must be those of a single pass, for host and device input."""
+    import torch
+    from librectify_b200.runner import Runner
+    from librectify_b200.synth import manhattan_frame
+    frames = torch.stack([manhattan_frame(70 + i, 640, 360, n_lines=30) for i in range(7)])
+    r = Runner(0, 3, 2)                                                     # 7 frames over 3 engines x 2 slots: ragged shards, several groups
+    tf1, info1 = r.rectify(frames.numpy(), 6.4)
+    tf3, info3 = r.rectify(frames.numpy(), 6.4, steps=3)
+    tfd, _ = r.rectify(frames.cuda(), 6.4, steps=2)
+    assert tf1.tobytes() == tf3.tobytes() == tfd.tobytes()
+    assert np.array_equal(info1["n_lines"], info3["n_lines"])
+    r.close()
