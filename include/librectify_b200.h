@@ -53,6 +53,10 @@ typedef struct lrb_frame_info {
 typedef struct lrb_engine lrb_engine;
 
 LRB_API const char * lrb_last_error(void);
+/* Return code of the last lrb_* (or drop-in) call on the calling thread: 0 = success.  The drop-in
+ * find_line_segment_groups returns nullptr both for "no segments" (reference src/interface.cpp:50-54,65-69) and for a
+ * CUDA failure; this tells them apart without parsing the message. */
+LRB_API int lrb_last_status(void);
 LRB_API const char * lrb_version(void);
 
 /* Seed of the sampler's mt19937 for engines created afterwards and for the drop-in API (the reference seeds from
@@ -70,7 +74,8 @@ LRB_API int  lrb_engine_slots(const lrb_engine * e);
 
 /* find_line_segment_groups for n_frames frames of equal size.
  *   frames        first pixel of frame 0; device memory for _device, host memory (pageable or pinned) for _host
- *   pitch         elements between rows (may be negative for _host with n_frames == 1, reference librectify.h:15-18)
+ *   pitch         elements between rows, |pitch| >= width; negative: every frame pointer addresses the frame's LAST row
+ *                 (bottom-up layout, reference librectify.h:15-18)
  *   frame_stride  elements between frames
  *   info          host array [n_frames]
  *   lines         host array [n_frames * lines_cap] or NULL; frame i's segments start at lines + i * lines_cap
@@ -81,6 +86,11 @@ LRB_API int lrb_detect_device(lrb_engine * e, const float * frames, int n_frames
 LRB_API int lrb_detect_host(lrb_engine * e, const float * frames, int n_frames, int width, int height,
                             long long pitch, long long frame_stride, float min_length,
                             lrb_frame_info * info, lrb_segment * lines, int lines_cap);
+
+/* Segments of slot `slot` of the engine's last launch group, copied straight from device memory: for frames whose list is
+ * longer than the caller's lines_cap (replaces a second pass over the frame; reference src/interface.cpp:75-79 sizes the
+ * result exactly).  Returns the number of segments copied (<= lines_cap) or a negative code. */
+LRB_API int lrb_fetch_lines(lrb_engine * e, int slot, lrb_segment * lines, int lines_cap);
 
 /* 8-bit frames: what the reference's demo does on the CPU before it calls the library —
  * cv::cvtColor(BGR2GRAY) (src/autorectify.cpp:340) and convertTo(CV_32F, 1/256.0) (src/autorectify.cpp:119) — moved to

@@ -57,6 +57,8 @@ def load_library(path: str | None = None):
     vp, ip, fp, ll = C.c_void_p, C.c_int, C.c_float, C.c_longlong
     lib.lrb_last_error.restype = C.c_char_p
     lib.lrb_version.restype = C.c_char_p
+    lib.lrb_last_status.restype = C.c_int
+    lib.lrb_fetch_lines.argtypes = [vp, ip, vp, ip]
     lib.lrb_set_seed.argtypes = [C.c_uint]; lib.lrb_set_seed.restype = None
     lib.lrb_engine_set_refine.argtypes = [vp, ip]
     for name in ("lrb_detect_host_u8", "lrb_detect_device_u8"):
@@ -130,9 +132,8 @@ def find_line_segment_groups(image: np.ndarray, min_length: float, refine: bool 
     if not ptr:
         if n.value != 0:
             raise LibrectifyError("null result with n_lines != 0")
-        msg = _err(lib)
-        if msg and ("CUDA" in msg or "failed" in msg or "capacity" in msg):
-            raise LibrectifyError(msg)
+        if lib.lrb_last_status() != 0:          # a failure, not the reference's "no segments" nullptr
+            raise LibrectifyError(_err(lib))
         return None
     out = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_byte)), shape=(n.value * 28,)).view(SEG_DTYPE).copy()
     p = C.c_void_p(ptr)
@@ -238,7 +239,19 @@ class Engine:
         self._check(fn(self.h, ptr, n, w, h, pitch, fs, C.c_float(min_length), info.ctypes.data, lines.ctypes.data, lines_cap))
         self.w, self.h_ = w, h
         if int(info["n_lines"].max(initial=0)) > lines_cap:
-            return self.detect(frames, min_length, int(info["n_lines"].max()))
+            if n > self.slots:                       # only the last launch group is still on the device
+                return self.detect(frames, min_length, int(info["n_lines"].max()))
+            out = []
+            for i in range(n):                       # long lists come straight from device memory (no second pass)
+                k = int(info["n_lines"][i])
+                if k <= lines_cap:
+                    out.append(lines[i, :k].copy()); continue
+                buf = np.zeros(k, SEG_DTYPE)
+                got = self.lib.lrb_fetch_lines(self.h, i, buf.ctypes.data, k)
+                if got != k:
+                    raise LibrectifyError(_err(self.lib))
+                out.append(buf)
+            return info, out
         return info, [lines[i, :info["n_lines"][i]].copy() for i in range(n)]
 
     def rectify(self, frames, min_length: float, cfg: np.ndarray | None = None):

@@ -57,18 +57,18 @@ LineSegment * find_line_segment_groups(InputPixelType * buffer, int width, int h
     lrb_engine_set_refine(e, refine ? 1 : 0);                         // interface.cpp:56-59
     lrb_frame_info info;
     LineSegment * res = nullptr;
-    // first pass copies at most 4096 segments; a frame with more is fetched again with the exact size
-    int cap = 4096;
-    std::vector<lrb_segment> tmp(cap);
-    int rc = lrb_detect_host(e, buffer, 1, width, height, stride, 0, min_length, &info, tmp.data(), cap);
-    if (rc == 0 && info.n_lines > cap) {
-        cap = info.n_lines; tmp.resize(cap);
-        rc = lrb_detect_host(e, buffer, 1, width, height, stride, 0, min_length, &info, tmp.data(), cap);
+    // the first 4096 segments travel with the control block; a longer list is fetched from device memory with its exact
+    // size — the frame is not processed a second time
+    const int head = 4096;
+    std::vector<lrb_segment> tmp(head);
+    int rc = lrb_detect_host(e, buffer, 1, width, height, stride, 0, min_length, &info, tmp.data(), head);
+    if (rc == 0 && info.n_lines > 0) {
+        res = new LineSegment[info.n_lines];                          // interface.cpp:75
+        if (info.n_lines <= head) std::memcpy(res, tmp.data(), sizeof(LineSegment) * info.n_lines);
+        else if (lrb_fetch_lines(e, 0, reinterpret_cast<lrb_segment *>(res), info.n_lines) != info.n_lines) { delete[] res; res = nullptr; }
     }
     pool().give(device, e);
-    if (rc != 0 || info.n_lines <= 0) return nullptr;                 // interface.cpp:50-54, 65-69
-    res = new LineSegment[info.n_lines];                              // interface.cpp:75
-    std::memcpy(res, tmp.data(), sizeof(LineSegment) * info.n_lines);
+    if (!res) return nullptr;                                         // interface.cpp:50-54, 65-69 (or a CUDA failure: lrb_last_status())
     *n_lines = info.n_lines;
     return res;
 }

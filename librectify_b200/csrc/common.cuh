@@ -9,8 +9,19 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <cstdlib>
+#include <mutex>
 
 namespace lrb {
+
+// Function attributes (dynamic shared-memory opt-in, carveout) and occupancy answers are PER DEVICE: a launcher that sets
+// them once per process leaves the second GPU of a single-process multi-GPU host without the opt-in.  once.run(fn) runs fn
+// the first time the calling launcher is used on the current device (thread-safe); dev() is the current device ordinal.
+struct PerDeviceOnce {
+    static constexpr int kMaxDev = 64;
+    std::once_flag flag[kMaxDev];
+    static int dev() { int d = 0; cudaGetDevice(&d); return d & (kMaxDev - 1); }
+    template <class F> int run(F && fn) { const int d = dev(); std::call_once(flag[d], fn); return d; }
+};
 
 // ---- reference configuration (src/config.h) ---------------------------------------------------------------------
 constexpr float kEps              = 1e-6f;    // config.h:10

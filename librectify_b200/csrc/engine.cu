@@ -30,15 +30,19 @@ using namespace lrb;
 namespace {
 
 thread_local std::string g_error;
+thread_local int g_status = 0;          // return code of the last C-ABI call on this thread (lrb_last_status)
 unsigned g_seed = 0;
 
 int fail(int code, const char * fmt, ...)
 {
     char buf[512];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
-    g_error = buf;
+    g_error = buf; g_status = code;
     return code;
 }
+
+// every C-ABI entry point starts clean: a stale message of an earlier failure on this thread must not be mistaken for this call's
+inline void begin_call() { g_error.clear(); g_status = 0; }
 
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(-2, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 
@@ -274,14 +278,21 @@ int copy_host_u8(lrb_engine * e, const unsigned char * src, int n, int w, int h,
     return 0;
 }
 
-void copy_host_frames(lrb_engine * e, const float * frames, int n, int w, int h, long long pitch, long long fstride, cudaStream_t st)
+int copy_host_frames(lrb_engine * e, const float * frames, int n, int w, int h, long long pitch, long long fstride, cudaStream_t st)
 {
+    // dense batch (rows and frames back to back, and the workspace rows need no padding): the whole group is one contiguous
+    // block -> ONE plain async copy instead of one 2-D copy per frame (a 32-frame 1080p group is a single 265 MB transfer)
+    if (pitch == w && e->pitch == w && fstride == (long long)w * h && e->plane == (size_t)w * h) {
+        CK(cudaMemcpyAsync(e->ws_img, frames, sizeof(float) * (size_t)w * h * n, cudaMemcpyHostToDevice, st));
+        return 0;
+    }
     for (int i = 0; i < n; ++i) {
         const float * base = frames + (long long)i * fstride; long long p = pitch;
         if (p < 0) { base = base + (long long)(h - 1) * p; p = -p; }
-        cudaMemcpy2DAsync(e->ws_img + (size_t)i * e->plane, sizeof(float) * e->pitch, base, sizeof(float) * (size_t)p,
-                          sizeof(float) * w, h, cudaMemcpyHostToDevice, st);
+        CK(cudaMemcpy2DAsync(e->ws_img + (size_t)i * e->plane, sizeof(float) * e->pitch, base, sizeof(float) * (size_t)p,
+                             sizeof(float) * w, h, cudaMemcpyHostToDevice, st));
     }
+    return 0;
 }
 
 // n_next > 0: the n_next frames that follow this group in the caller's host buffer form the next group (host input only)
@@ -360,8 +371,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         CK(cudaStreamWaitEvent(e->st, e->ev_copy_done, 0));              // copied while the previous group was computing
         e->pre_copied = false;
     } else {
-        copy_host_frames(e, frames, n, w, h, pitch, fstride, e->st);
-        CK(cudaGetLastError());
+        if (int r = copy_host_frames(e, frames, n, w, h, pitch, fstride, e->st)) return r;
     }
     // ---- detection ---------------------------------------------------------------------------------------------------
     stage(LRB_T_GRAD);
@@ -370,7 +380,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     if (!on_device && !u8.channels && n_next > 0 && !no_prefetch) {       // the image workspace is free again after K1
         CK(cudaEventRecord(e->ev_k1_done, e->st));
         CK(cudaStreamWaitEvent(e->st_copy, e->ev_k1_done, 0));
-        copy_host_frames(e, frames + (long long)n * fstride, n_next, w, h, pitch, fstride, e->st_copy);
+        if (int r = copy_host_frames(e, frames + (long long)n * fstride, n_next, w, h, pitch, fstride, e->st_copy)) return r;
         CK(cudaEventRecord(e->ev_copy_done, e->st_copy));
         e->pre_copied = true;
     }
@@ -463,11 +473,13 @@ int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, i
            long long fstride, float min_length, lrb_frame_info * info, lrb_segment * lines, int lines_cap,
            const lrb_config * cfg, int n_cfg, lrb_transform * tf, U8Src u8 = U8Src())
 {
+    begin_call();
     if (!e) return fail(-1, "null engine");
     if (n_frames < 0 || (!frames && !u8.channels)) return fail(-1, "bad arguments");
     if (u8.channels && (!u8.data || (u8.channels != 1 && u8.channels != 3) || pitch < (long long)w * u8.channels))
         return fail(-1, "8-bit input: 1 (gray) or 3 (BGR) channels, pitch in bytes >= width * channels");
-    if (pitch < 0 && n_frames != 1) return fail(-1, "negative pitch is only supported for a single frame");
+    // float input: |pitch| >= width; a negative pitch means every frame pointer addresses its LAST row (reference librectify.h:15-18)
+    if (!u8.channels && (pitch < 0 ? -pitch : pitch) < (long long)w) return fail(-1, "pitch (%lld elements) smaller than a row of %d pixels", pitch, w);
     std::vector<lrb_segment> tmp;
     for (int f0 = 0; f0 < n_frames; f0 += e->slots) {
         const int n = std::min(e->slots, n_frames - f0);

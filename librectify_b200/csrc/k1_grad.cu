@@ -19,6 +19,7 @@
 // tile keeping five partially accumulated output rows in registers, and writes dx/dy/mag as 128-bit and bin as
 // 32-bit coalesced stores.  HBM traffic is the compulsory 4 B read + 13 B written per pixel.
 #include <cstdlib>
+#include <cstdio>
 #include "common.cuh"
 #include "tma.cuh"
 #include "kernels.h"
@@ -347,24 +348,24 @@ void launch_grad(const CUtensorMap & tmap, const Planes & P, FrameCtrl * ctrl, i
     // per thread; the taller strip amortises the 4-row halo (products of 20 input rows per 16 output rows instead of 12 per 8)
     static const int cfg = [] { const char * v = getenv("LRB_K1_CFG"); return v ? atoi(v) : 1; }();
     dim3 grid((P.w + K1_TW - 1) / K1_TW, (P.h + 63) / 64, n_slots);
-    if (cfg >= 10) {                            // persistent, double-buffered
+    if (cfg >= 10) {                            // LRB_K1_CFG=10: persistent, double-buffered — the documented alternative (profiles/r1_sweeps.md)
         auto kern = k_grad5x5_bin_persistent<8, 8, 2>;
         constexpr int smem = 2 * (64 + 4) * K1_SW * (int)sizeof(float) + 64 + 8 * 8 + 128;
-        static int n_sm = 0;
-        if (n_sm == 0) {
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-            cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
-            int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-        }
+        static PerDeviceOnce once; static int n_sm[PerDeviceOnce::kMaxDev];
+        const int d = once.run([&] {
+            const int dv = PerDeviceOnce::dev();
+            cudaError_t e1 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
+            if (e1 != cudaSuccess || e2 != cudaSuccess) fprintf(stderr, "[lrb] K1: shared-memory opt-in failed on device %d\n", dv);
+            n_sm[dv] = 148; cudaDeviceGetAttribute(&n_sm[dv], cudaDevAttrMultiProcessorCount, dv);
+        });
         const int n_tiles = (int)(grid.x * grid.y * grid.z);
-        const int blocks = n_tiles < 2 * n_sm ? n_tiles : 2 * n_sm;
+        const int blocks = n_tiles < 2 * n_sm[d] ? n_tiles : 2 * n_sm[d];
         kern<<<blocks, 256, smem, st>>>(tmap, P, ctrl, tma_x, tma_y, (int)grid.x, (int)grid.y, n_tiles);
         return;
     }
-    if (cfg == 0)      k_grad5x5_bin<8, 8, 2><<<grid, 256, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
-    else if (cfg == 2) k_grad5x5_bin<16, 4, 5><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
-    else if (cfg == 3) k_grad5x5_bin<16, 4, 6><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
-    else             { LRB_CARVEOUT((k_grad5x5_bin<16, 4, 4>)); k_grad5x5_bin<16, 4, 4><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y); }
+    LRB_CARVEOUT((k_grad5x5_bin<16, 4, 4>));
+    k_grad5x5_bin<16, 4, 4><<<grid, 128, 0, st>>>(tmap, P, ctrl, tma_x, tma_y);
 }
 
 int grad_tile_w() { return K1_SW; }

@@ -17,6 +17,7 @@
 // sort: bucket scan -> scatter -> exact rank inside the (tiny) bucket by counting.  The rank is the seed's flood
 // priority and its slot in every per-seed array.
 #include <cstdlib>
+#include <cstdio>
 #include "common.cuh"
 #include "tma.cuh"
 #include "kernels.h"
@@ -250,48 +251,6 @@ k_nms5x5_seeds_persistent(const __grid_constant__ CUtensorMap tmap_mag, const __
     }
 }
 
-// Two vertically adjacent tiles per CTA (LRB_K2_CFG=20): both tiles' boxes are issued at once, so the second tile's HBM
-// latency hides behind the first tile's arithmetic, while the CTA stays short-lived (the persistent form's long-lived CTAs are
-// what costs job throughput when several engines share the GPU).
-template <int K2_RPT, int MINB>
-__global__ void __launch_bounds__(32 * (K2_TH / K2_RPT), MINB)
-k_nms5x5_seeds_pair(const __grid_constant__ CUtensorMap tmap_mag, const __grid_constant__ CUtensorMap tmap_bin,
-                    Planes P, Seeds S, FrameCtrl * ctrl, int tma_x, int tma_y, int tiles_y)
-{
-    extern __shared__ unsigned char k2_smem_raw[];
-    unsigned char * sm = k2_smem_raw + ((128u - (smem_u32(k2_smem_raw) & 127u)) & 127u);
-    uint64_t * bar = reinterpret_cast<uint64_t *>(sm + K2_STAGE_OFF_BIN + 2 * K2_BIN_BYTES);
-    int * s_cnt = reinterpret_cast<int *>(bar + 2);
-    int * s_base = s_cnt + 2;
-    const int slot = blockIdx.z;
-    const int x0 = blockIdx.x * K2_TW;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int n_mine = min(2, tiles_y - 2 * (int)blockIdx.y);
-    if (threadIdx.x == 0) {
-        mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init();
-        s_cnt[0] = 0; s_cnt[1] = 0;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        for (int k = 0; k < n_mine; ++k) {
-            const int y0 = (2 * blockIdx.y + k) * K2_TH;
-            mbar_arrive_expect_tx(&bar[k], K2_MH * K2_MW * 4 + K2_BH * K2_BW);
-            tma_load_3d(sm + k * (K2_MH * K2_MW * 4), &tmap_mag, x0 - 4 + tma_x, y0 - 2 + tma_y, slot, &bar[k]);
-            tma_load_3d(sm + K2_STAGE_OFF_BIN + k * K2_BIN_BYTES, &tmap_bin, x0 - 16 + tma_x, y0 - 1 + tma_y, slot, &bar[k]);
-        }
-    }
-    const float gmax = __uint_as_float(ctrl[slot].gmax_bits);
-    const float thr = __fmul_rn(gmax, kSeedFactor);
-    const float tup = __uint_as_float(__float_as_uint(thr) + 1u);
-    for (int k = 0; k < n_mine; ++k) {
-        const int y0 = (2 * blockIdx.y + k) * K2_TH;
-        const float * tm = reinterpret_cast<const float *>(sm + k * (K2_MH * K2_MW * 4));
-        mbar_wait(&bar[k], 0);
-        const unsigned peakmask = nms_tile<K2_RPT>(tm, sm + K2_STAGE_OFF_BIN + k * K2_BIN_BYTES, P, slot, x0, y0, tup, lane, warp);
-        nms_append<K2_RPT>(peakmask, tm, &s_cnt[k], s_base, P, S, ctrl, slot, x0, y0, gmax, thr, lane, warp);
-    }
-}
-
 // exclusive scan of the bucket histogram; one block of 1024 threads per frame, 4 buckets per thread
 __global__ void __launch_bounds__(1024) k_seed_scan(Seeds S, FrameCtrl * ctrl)
 {
@@ -399,42 +358,31 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
 {
     dim3 grid((P.w + K2_TW - 1) / K2_TW, (P.h + K2_TH - 1) / K2_TH, n_slots);
     static const int cfg = [] { const char * v = getenv("LRB_K2_CFG"); return v ? atoi(v) : 15; }();
-    if (cfg >= 20) {                            // two tiles per CTA
-        auto kern = (cfg >= 21) ? k_nms5x5_seeds_pair<8, 3> : k_nms5x5_seeds_pair<8, 4>;
-        static bool once = false;
-        if (!once) {
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_PERSIST_SMEM);
-            // three CTAs per SM under a 164 KB split: a kernel that asks for the maximum split leaves the SMs with a 28 KB L1,
-            // and the other engines' flood kernels, which share those SMs, lose a fifth of their speed
-            if (cfg == 22) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
-            once = true;
-        }
-        dim3 g2(grid.x, (grid.y + 1) / 2, grid.z);
-        LRB_CARVEOUT(kern);
-        kern<<<g2, 128, K2_PERSIST_SMEM, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y, (int)grid.y);
-        return;
-    }
-    if (cfg >= 10) {                            // persistent, double-buffered
-        auto kern = (cfg == 11 || cfg == 15) ? k_nms5x5_seeds_persistent<8, 3> : (cfg == 12) ? k_nms5x5_seeds_persistent<4, 2> : k_nms5x5_seeds_persistent<8, 4>;
-        const int threads = (cfg == 12) ? 256 : 128;
-        static int per_sm = 0, n_sm = 148;
-        if (per_sm == 0) {
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_PERSIST_SMEM);
-            if (cfg == 15) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, K2_PERSIST_SMEM) != cudaSuccess || per_sm < 1) per_sm = 1;
-            int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-        }
+    if (cfg >= 10) {                            // persistent, double-buffered (default: three CTAs per SM under a 66 % split)
+        auto kern = k_nms5x5_seeds_persistent<8, 3>;
+        const int threads = 128;
+        static PerDeviceOnce once; static int per_sm[PerDeviceOnce::kMaxDev], n_sm[PerDeviceOnce::kMaxDev]; static cudaError_t attr_err[PerDeviceOnce::kMaxDev];
+        const int d = once.run([&] {
+            const int dv = PerDeviceOnce::dev();
+            cudaError_t e1 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_PERSIST_SMEM);
+            // a kernel that asks for the maximum split leaves the SMs with a 28 KB L1, and the other engines' flood kernels,
+            // which share those SMs, lose a fifth of their speed: three CTAs per SM under a 66 % split
+            cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 66);
+            attr_err[dv] = e1 != cudaSuccess ? e1 : e2;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm[dv], kern, threads, K2_PERSIST_SMEM) != cudaSuccess || per_sm[dv] < 1) per_sm[dv] = 1;
+            n_sm[dv] = 148; cudaDeviceGetAttribute(&n_sm[dv], cudaDevAttrMultiProcessorCount, dv);
+        });
+        if (attr_err[d] != cudaSuccess) fprintf(stderr, "[lrb] K2: shared-memory opt-in failed on device %d: %s (the launch below will fail)\n", d, cudaGetErrorString(attr_err[d]));
         const int n_tiles = (int)(grid.x * grid.y * grid.z);
-        const int use_per_sm = (cfg == 13) ? 2 : (cfg == 14) ? 1 : (cfg == 15) ? 3 : per_sm;
-        const int blocks = n_tiles < n_sm * use_per_sm ? n_tiles : n_sm * use_per_sm;
+        const int use_per_sm = per_sm[d] < 3 ? per_sm[d] : 3;
+        const int blocks = n_tiles < n_sm[d] * use_per_sm ? n_tiles : n_sm[d] * use_per_sm;
         LRB_CARVEOUT(kern);
         kern<<<blocks, threads, K2_PERSIST_SMEM, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y, (int)grid.x, (int)grid.y, n_tiles);
         return;
     }
-    if (cfg == 1)      k_nms5x5_seeds<4, 4><<<grid, 256, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
-    else if (cfg == 4) k_nms5x5_seeds<8, 8><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
-    else if (cfg == 0) k_nms5x5_seeds<8, 5><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
-    else             { LRB_CARVEOUT((k_nms5x5_seeds<8, 6>)); k_nms5x5_seeds<8, 6><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y); }
+    // LRB_K2_CFG=2: the one-shot form (one tile per CTA) — the documented alternative, see profiles/r1_sweeps.md
+    LRB_CARVEOUT((k_nms5x5_seeds<8, 6>));
+    k_nms5x5_seeds<8, 6><<<grid, 128, 0, st>>>(tmap_mag, tmap_bin, P, S, ctrl, tma_x, tma_y);
 }
 
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st)

@@ -576,11 +576,13 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
     // register budget of the flood kernel: MINB resident CTAs per SM (LRB_FLOOD_MINB=4|5|6|8 for experiments; 4 loads a tile's 32 rows in one batch)
     static const int minb = [] { const char * v = getenv("LRB_FLOOD_MINB"); return v ? atoi(v) : 4; }();
     auto kern = (minb >= 8) ? k_flood_round<8, 16> : (minb == 6) ? k_flood_round<6, 16> : (minb == 4) ? k_flood_round<4, 32> : (minb == 7) ? k_flood_round<6, 32> : (minb == 3) ? k_flood_round<5, 32> : k_flood_round<5, 16>;
-    static int per_sm = 0;
-    if (per_sm == 0) {
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FL_WARPS * 32, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
-    }
-    int n_sm = 148; { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
+    static PerDeviceOnce once; static int per_sm_d[PerDeviceOnce::kMaxDev], n_sm_d[PerDeviceOnce::kMaxDev];
+    const int d = once.run([&] {
+        const int dv = PerDeviceOnce::dev();
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_d[dv], kern, FL_WARPS * 32, 0) != cudaSuccess || per_sm_d[dv] < 1) per_sm_d[dv] = 4;
+        n_sm_d[dv] = 148; cudaDeviceGetAttribute(&n_sm_d[dv], cudaDevAttrMultiProcessorCount, dv);
+    });
+    const int per_sm = per_sm_d[d], n_sm = n_sm_d[d];
     // LRB_FLOOD_SUB=k floods k frames at a time (all rounds of one sub-batch, then the next) to keep their planes L2
     // resident.  Measured on B200 (gpurun_out/sweep4.log): slower at every k < n_slots — a round is bound by its longest
     // flood chain, not by bandwidth, so more frames in flight win — hence the default is one batch of all slots.

@@ -65,7 +65,8 @@ __global__ void __launch_bounds__(1024) k_filter_model(Comps K, Lines L, FrameCt
             keep = (len > ml) && (s.err < kLineMaxErr);
         }
         int total;
-        const int pos = s_base + block_scan_flag(keep, wsum, total);
+        const int base = s_base;                 // read before the barriers inside the scan: thread 0 advances s_base right after it
+        const int pos = base + block_scan_flag(keep, wsum, total);
         if (keep) {
             if (pos < L.cap) {
                 seg[pos] = s;
