@@ -197,6 +197,13 @@ LRB_API void lrb_profile_read(lrb_engine * e, double * ms, long long * groups, l
 LRB_API long long lrb_sample_pairs(lrb_engine * e, int n, int count, int * pairs);            /* plain sequential walk */
 LRB_API long long lrb_sample_pairs_parallel(lrb_engine * e, int n, int count, int * pairs);   /* speculative workers + stitch */
 
+/* Known-answer entry point of the tie-order replay (k3_replay.cu): the reference sorts its peak list with std::sort on the
+ * magnitude alone (reference src/filter.cpp:188), so the order of exact ties is what libstdc++'s introsort leaves.  `vals` is
+ * a list in the order std::sort would receive it; order[j] receives the index (into vals) of the element that
+ * std::sort(vals, vals + n, greater-by-value) puts at place j.  depth_override < 0: the real depth limit 2*floor(log2 n);
+ * >= 0 forces the heap-sort branch early (tests).  Returns the number of partition steps replayed, negative on error. */
+LRB_API long long lrb_sort_replay(lrb_engine * e, const float * vals, int n, int depth_override, int * order);
+
 #ifdef __cplusplus
 }
 #endif

@@ -86,6 +86,7 @@ def load_library(path: str | None = None):
     lib.lrb_profile_enable.argtypes = [vp, ip]; lib.lrb_profile_enable.restype = None
     lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None
     lib.lrb_profile_read.argtypes = [vp, vp, vp, vp]; lib.lrb_profile_read.restype = None
+    lib.lrb_sort_replay.argtypes = [vp, vp, ip, ip, vp]; lib.lrb_sort_replay.restype = ll
     lib.lrb_sample_pairs.argtypes = [vp, ip, ip, vp]; lib.lrb_sample_pairs.restype = ll
     lib.lrb_sample_pairs_parallel.argtypes = [vp, ip, ip, vp]; lib.lrb_sample_pairs_parallel.restype = ll
     # the drop-in symbols (reference names)
@@ -400,6 +401,16 @@ class Engine:
         raw = self.fetch("ransac", slot)
         return dict(winner=raw[:4].copy(), best_h=raw[4:16].view(np.float32).reshape(4, 3).copy(),
                     refined=raw[16:28].view(np.float32).reshape(4, 3).copy())
+
+    def sort_replay(self, vals: np.ndarray, depth_override: int = -1):
+        """order in which libstdc++ std::sort (comparator: value descending) leaves ``vals`` — indices into vals; also the
+        number of partition steps the device replayed (k3_replay.cu)."""
+        v = np.ascontiguousarray(vals, np.float32)
+        order = np.zeros(len(v), np.int32)
+        steps = self.lib.lrb_sort_replay(self.h, v.ctypes.data, len(v), int(depth_override), order.ctypes.data)
+        if steps < 0:
+            raise LibrectifyError(_err(self.lib))
+        return order, int(steps)
 
     def sample_pairs(self, n: int, count: int, parallel: bool = False):
         pairs = np.zeros((count, 2), np.int32)

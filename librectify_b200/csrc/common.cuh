@@ -68,6 +68,8 @@ constexpr int kMaxRounds = 96;
 struct FrameCtrl {
     unsigned gmax_bits;        // max gradient magnitude (float bits, mag >= 0 so uint order == float order)
     int n_seeds;               // peaks emitted by the NMS kernel
+    int n_tied;                // seeds whose magnitude equals another seed's exactly (their order needs the std::sort replay)
+    int replay_steps;          // partition steps replayed for this frame (statistics)
     int seed_overflow;         // more peaks than capacity
     int flood_overflow;        // a flood ran out of queue / lost-list space in the speculative rounds
     int n_comp;                // kept components (size > kComponentMinSize)
@@ -130,6 +132,14 @@ struct Seeds {                  // per slot: s * cap
     int * size;
     int * list_head;                          // first pool chunk of the seed's tentative pixel list (this round)
     int * hist; int * start; int * cursor;    // kSeedBuckets each per slot
+    // raster order of the peaks and the std::sort replay (k3_replay.cu): the reference sorts its peak list, which is in raster
+    // order, with std::sort (reference src/filter.cpp:174-188) — unstable, so the order of exact-magnitude ties is whatever
+    // introsort's partitions leave behind
+    int rows, roww;                           // frame height (per-slot stride of the three row arrays) and width
+    int * rowhist; int * rowstart; int * rowcursor;   // peaks per image row -> first raster position of the row's peaks
+    int * rb_col;                             // per slot: cap; columns of the peaks, bucketed by row
+    uint2 * rp_el;                            // per slot: cap; the peak list as std::sort sees it: x = key (dense rank of the magnitude, ties share it), y = tied << 31 | rank by (magnitude desc, raster asc)
+    int4 * rp_q;                              // per slot: cap; work list of the replay (segment first, last, depth left, tied elements inside)
 };
 
 struct Comps {                  // per slot

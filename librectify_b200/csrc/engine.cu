@@ -171,6 +171,9 @@ int ensure_workspace(lrb_engine * e, int w, int h)
         e->S.list_head = carve<int>(p, (size_t)cap_seeds * G);
         e->S.hist = carve<int>(p, (size_t)kSeedBuckets * G); e->S.start = carve<int>(p, (size_t)kSeedBuckets * G);
         e->S.cursor = carve<int>(p, (size_t)kSeedBuckets * G);
+        e->S.rowhist = carve<int>(p, (size_t)h * G); e->S.rowstart = carve<int>(p, (size_t)h * G); e->S.rowcursor = carve<int>(p, (size_t)h * G);
+        e->S.rb_col = carve<int>(p, (size_t)cap_seeds * G);
+        e->S.rp_el = carve<uint2>(p, (size_t)cap_seeds * G); e->S.rp_q = carve<int4>(p, (size_t)cap_seeds * G);
         e->K.rank = carve<int>(p, (size_t)cap_comp * G); e->K.off = carve<int>(p, (size_t)cap_comp * G);
         e->K.size = carve<int>(p, (size_t)cap_comp * G);
         e->K.px = carve<unsigned>(p, cap_px * G); e->K.val = carve<float>(p, cap_px * G);
@@ -201,6 +204,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     e->S.win_min = kFloodWindowMin; e->S.win_div = kFloodWindowDiv;
     if (const char * v = getenv("LRB_WINDOW_MIN")) e->S.win_min = std::max(1, atoi(v));
     if (const char * v = getenv("LRB_WINDOW_DIV")) e->S.win_div = std::max(1, atoi(v));
+    e->S.rows = h; e->S.roww = w;
     e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->K.cap_pool = (int)std::min<size_t>(cap_pool, 0x7fffffe0); e->L.cap = cap_lines;
     e->K.big_slots = kBigSlots; e->K.big_cap = big_cap; e->K.big_bytes = big_bytes;
     CK(cudaMemsetAsync(e->arena, 0, bytes, e->st));

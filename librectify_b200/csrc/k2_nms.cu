@@ -147,6 +147,7 @@ __device__ __forceinline__ void nms_append(unsigned peakmask, const float * tmag
     const float scale = __fdiv_rn((float)kSeedBuckets, __fsub_rn(gmax, thr));
     unsigned * us_mag = S.us_mag + (size_t)slot * S.cap; unsigned * us_idx = S.us_idx + (size_t)slot * S.cap;
     int * hist = S.hist + (size_t)slot * kSeedBuckets;
+    int * rowhist = S.rowhist + (size_t)slot * S.rows;
     while (peakmask) {
         const int b = __ffs(peakmask) - 1;
         peakmask &= peakmask - 1;
@@ -156,6 +157,7 @@ __device__ __forceinline__ void nms_append(unsigned peakmask, const float * tmag
             us_mag[o] = __float_as_uint(m);
             us_idx[o] = (unsigned)((y0 + ty0 + j) * P.w + (xq + c));      // raster index in the dense W x H image
             atomicAdd(&hist[seed_bucket_scaled(m, thr, scale)], 1);
+            atomicAdd(&rowhist[y0 + ty0 + j], 1);                         // peaks per image row: raster position of every peak (k_seed_rank)
         } else {
             ctrl[slot].seed_overflow = 1;
         }
@@ -277,6 +279,28 @@ __global__ void __launch_bounds__(1024) k_seed_scan(Seeds S, FrameCtrl * ctrl)
     const int ex = incl - mine + (warp ? wsum[warp - 1] : 0);
     *reinterpret_cast<int4 *>(start + 4 * t) = make_int4(ex, ex + h.x, ex + h.x + h.y, ex + h.x + h.y + h.z);
     *reinterpret_cast<int4 *>(cursor + 4 * t) = make_int4(0, 0, 0, 0);
+    {   // exclusive scan of the per-row peak counts: rowstart[r] = raster position of the first peak of row r
+        __syncthreads();                        // wsum is reused
+        const int rows = S.rows, per = (rows + 1023) / 1024;
+        const int * rh = S.rowhist + (size_t)slot * rows; int * rs = S.rowstart + (size_t)slot * rows; int * rc = S.rowcursor + (size_t)slot * rows;
+        const int r0 = t * per, r1 = min(rows, r0 + per);
+        int sum = 0;
+        for (int r = r0; r < r1; ++r) sum += rh[r];
+        int inc = sum;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += v; }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int v = wsum[lane];
+#pragma unroll
+            for (int s = 1; s < 32; s <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, s); if (lane >= s) v += u; }
+            wsum[lane] = v;
+        }
+        __syncthreads();
+        int run = inc - sum + (warp ? wsum[warp - 1] : 0);
+        for (int r = r0; r < r1; ++r) { rs[r] = run; run += rh[r]; rc[r] = 0; }
+    }
     if (t == 0) {
         if (ctrl[slot].n_seeds > S.cap) { ctrl[slot].n_seeds = S.cap; ctrl[slot].seed_overflow = 1; }
         const int ns = ctrl[slot].n_seeds;
@@ -298,8 +322,12 @@ __global__ void __launch_bounds__(256) k_seed_scatter(Seeds S, FrameCtrl * ctrl)
     const unsigned m = S.us_mag[so + i];
     const int d = seed_bucket(__uint_as_float(m), thr, gmax);
     const int pos = S.start[bo + d] + atomicAdd(&S.cursor[bo + d], 1);
+    const unsigned ix = S.us_idx[so + i];
     S.b_mag[so + pos] = m;
-    S.b_idx[so + pos] = S.us_idx[so + i];
+    S.b_idx[so + pos] = ix;
+    const int row = (int)(ix / (unsigned)S.roww), col = (int)(ix - (unsigned)row * (unsigned)S.roww);
+    const size_t ro = (size_t)slot * S.rows + row;
+    S.rb_col[so + S.rowstart[ro] + atomicAdd(&S.rowcursor[ro], 1)] = col;
 }
 
 // exact rank inside the bucket by counting, then per-seed flood parameters
@@ -318,13 +346,24 @@ __global__ void __launch_bounds__(256) k_seed_rank(Planes P, Seeds S, FrameCtrl 
     // the in-bucket rank costs O(bucket^2); an input with tens of thousands of (nearly) equal magnitudes is rejected
     // loudly instead of occupying the GPU for seconds
     if (hi - lo > 16384) { ctrl[slot].seed_overflow = 2; return; }
-    int before = 0;
+    int greater = 0, eq_before = 0, eq_total = 0;
     for (int j = lo; j < hi; ++j) {
         const unsigned mj = S.b_mag[so + j], ij = S.b_idx[so + j];
-        before += (mj > m) || (mj == m && ij < ix);          // positive floats: bit order == value order
+        greater += (mj > m);                                  // positive floats: bit order == value order
+        eq_total += (mj == m); eq_before += (mj == m && ij < ix);
     }
-    const int rank = lo + before;
+    const int key = lo + greater;                             // dense rank of the magnitude: exact ties share it
+    const int rank = key + eq_before;                         // (magnitude desc, raster asc); final unless the peak is tied (k_seed_replay)
     const int r = ix / P.w, c = ix - r * P.w;
+    {   // the peak's place in the reference's peak list before the sort = its raster position (filter.cpp:174-186, single thread)
+        const size_t ro = (size_t)slot * S.rows + r;
+        const int rs = S.rowstart[ro], re = rs + S.rowhist[ro];
+        int rp = rs;
+        for (int j = rs; j < re; ++j) rp += (S.rb_col[so + j] < c);
+        const unsigned tied = eq_total > 1 ? 0x80000000u : 0u;
+        S.rp_el[so + rp] = make_uint2((unsigned)key, tied | (unsigned)rank);
+        if (tied) atomicAdd(&ctrl[slot].n_tied, 1);
+    }
     const size_t po = (size_t)slot * P.stride + (size_t)r * P.pitch + c;
     const int b = P.bin[po];
     S.idx[so + rank] = ix;
@@ -344,6 +383,8 @@ __global__ void __launch_bounds__(256) k_frame_init(Seeds S, FrameCtrl * ctrl)
     for (int i = threadIdx.x; i < (int)(sizeof(FrameCtrl) / sizeof(int)); i += blockDim.x) c[i] = 0;
     int * hist = S.hist + (size_t)slot * kSeedBuckets;
     for (int i = threadIdx.x; i < kSeedBuckets; i += blockDim.x) hist[i] = 0;
+    int * rowhist = S.rowhist + (size_t)slot * S.rows;
+    for (int i = threadIdx.x; i < S.rows; i += blockDim.x) rowhist[i] = 0;
 }
 
 } // namespace
@@ -392,6 +433,7 @@ void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int 
     dim3 grid((seeds_hint + 255) / 256, n_slots);
     k_seed_scatter<<<grid, 256, 0, st>>>(S, ctrl);
     k_seed_rank<<<grid, 256, 0, st>>>(P, S, ctrl);
+    launch_seed_replay(P, S, ctrl, n_slots, -1, true, st);
 }
 
 void nms_tile_dims(int * mw, int * mh, int * bw, int * bh) { *mw = K2_MW; *mh = K2_MH; *bw = K2_BW; *bh = K2_BH; }

@@ -16,6 +16,8 @@ void launch_nms(const CUtensorMap & tmap_mag, const CUtensorMap & tmap_bin, cons
                 FrameCtrl * ctrl, int n_slots, int tma_x, int tma_y, cudaStream_t st);
 void launch_seed_order(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int seeds_hint, cudaStream_t st);
 void nms_tile_dims(int * mw, int * mh, int * bw, int * bh);
+// k3_replay.cu: canonical order of exact-magnitude ties = what libstdc++ std::sort leaves (replay of introsort's partitions)
+void launch_seed_replay(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int depth_override, bool fixup, cudaStream_t st);
 // k4_flood.cu
 int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int seeds_hint,
                          int round_begin, int round_end, unsigned epoch_first, cudaStream_t st);

@@ -273,6 +273,13 @@ class Oracle(_StageLib):
             make_all("oracle")
         super().__init__(path)
 
+    def std_sort_order(self, vals, depth_override=-1):
+        """order in which std::sort with find_peaks' comparator (reference src/filter.cpp:188) leaves ``vals``"""
+        v = np.ascontiguousarray(vals, np.float32)
+        order = np.zeros(len(v), np.int32)
+        self.lib.orc_std_sort_order(_fp(v), C.c_int(len(v)), C.c_int(depth_override), _ip(order))
+        return order
+
 
 def ref_available(flavour="canon"):
     return os.path.exists(os.path.join(REF_DIR, f"librectify_{flavour}.so"))

@@ -1057,4 +1057,21 @@ int orc_sizeof(int which)
     return -1;
 }
 
+/* Known answers for the tie-order replay of the CUDA path (librectify_b200/csrc/k3_replay.cu): the order in which
+ * std::sort with find_peaks' comparator (reference src/filter.cpp:188, element = {int i, j; float v}) leaves a value list.
+ * order[j] = index into vals of the element at place j.  depth_override >= 0 calls libstdc++'s introsort loop with that
+ * depth limit (then the final insertion sort), to reach the heap-sort branch on small inputs. */
+void orc_std_sort_order(const float * vals, int n, int depth_override, int * order)
+{
+    struct Peak { int i, j; float v; };
+    vector<Peak> peaks(n);
+    for (int k = 0; k < n; ++k) peaks[k] = Peak{k, 0, vals[k]};
+    auto cmp = [](const Peak & a, const Peak & b) { return a.v > b.v; };
+    if (depth_override < 0) std::sort(peaks.begin(), peaks.end(), cmp);
+    else if (n > 0) {
+        std::__introsort_loop(peaks.begin(), peaks.end(), (long)depth_override, __gnu_cxx::__ops::__iter_comp_iter(cmp));
+        std::__final_insertion_sort(peaks.begin(), peaks.end(), __gnu_cxx::__ops::__iter_comp_iter(cmp));
+    }
+    for (int k = 0; k < n; ++k) order[k] = peaks[k].i;
+}
 } // extern "C"

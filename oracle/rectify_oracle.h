@@ -55,6 +55,8 @@ void orc_compute_rectification_transform_from_vp(int w, int h, const OrcPoint * 
                                                  OrcImageTransform * out);
 void orc_fit_vanishing_point(const OrcLineSegment * lines, int n, int group, OrcPoint * out);
 int  orc_sizeof(int which);
+/* order in which std::sort (find_peaks' comparator, reference src/filter.cpp:188) leaves `vals`: known answers for k3_replay.cu */
+void orc_std_sort_order(const float * vals, int n, int depth_override, int * order);
 
 /* extra trace used by the GPU parity tests: full RANSAC trace of one estimate_line_pencils call.
  * samples: [4][T][2] positions into the observation list of each solve, scores: [4][T] (-1 = rejected by
