@@ -148,6 +148,31 @@ LRB_API int lrb_rectify_host(lrb_engine * e, const float * frames, int n_frames,
                              long long pitch, long long frame_stride, float min_length,
                              const lrb_config * cfg, int n_cfg, lrb_transform * transforms, lrb_frame_info * info);
 
+/* ---- multi-GPU batch entry (north_star: "a batch of independent images shards naturally across the 8 GPUs of
+ * one box, one stream set per GPU ... at most a host-side gather of per-image ImageTransforms") ------------------------------
+ * A pool owns engines_per_device engines (stream set + workspace of `slots` frames each) on every listed device.  A call
+ * shards its frames: frame i of B -> device floor(i * G / B) (contiguous blocks), inside a device contiguous blocks per
+ * engine, one host thread per engine (cudaSetDevice per thread), no collective; transforms and infos are written at the
+ * frame's own index (the gather).  The config of frame i is cfg[i % n_cfg].  passes > 1 streams the same batch through
+ * `passes` times without joining the engines in between (a benchmark's K steps); the results of the last pass are returned.
+ *   _host      frames in host memory (pageable or pinned), pitch / frame_stride in elements
+ *   _host_u8   8-bit gray or BGR frames in host memory, pitch / frame_stride in bytes
+ *   _device    shards[d] = first pixel of the counts[d] frames resident on devices[d]; results in shard order */
+typedef struct lrb_pool lrb_pool;
+LRB_API int  lrb_pool_create(const int * devices, int n_devices, int engines_per_device, int slots, lrb_pool ** out);
+LRB_API void lrb_pool_destroy(lrb_pool * p);
+LRB_API int  lrb_pool_engines(const lrb_pool * p);
+LRB_API lrb_engine * lrb_pool_engine(lrb_pool * p, int i);     /* engine i (device-major), e.g. for the stage timers */
+LRB_API int lrb_pool_rectify_host(lrb_pool * p, const float * frames, int n_frames, int width, int height, long long pitch,
+                                  long long frame_stride, float min_length, const lrb_config * cfg, int n_cfg,
+                                  lrb_transform * transforms, lrb_frame_info * info, int passes);
+LRB_API int lrb_pool_rectify_host_u8(lrb_pool * p, const unsigned char * frames, int n_frames, int width, int height, int channels,
+                                     long long pitch, long long frame_stride, float min_length, const lrb_config * cfg, int n_cfg,
+                                     lrb_transform * transforms, lrb_frame_info * info, int passes);
+LRB_API int lrb_pool_rectify_device(lrb_pool * p, const float * const * shards, const int * counts, int width, int height,
+                                    long long pitch, long long frame_stride, float min_length, const lrb_config * cfg, int n_cfg,
+                                    lrb_transform * transforms, lrb_frame_info * info, int passes);
+
 /* Host-side corner solve on caller-provided segments (pointer form of compute_rectification_transform etc.). */
 LRB_API void lrb_compute_transform(const lrb_segment * lines, int n_lines, int width, int height,
                                    const lrb_config * cfg, lrb_transform * out);
@@ -191,6 +216,12 @@ LRB_API void lrb_profile_enable(lrb_engine * e, int on);
 LRB_API void lrb_profile_reset(lrb_engine * e);
 /* ms[LRB_T_COUNT]: summed device milliseconds per stage; groups: launch groups timed; kernels: kernels launched */
 LRB_API void lrb_profile_read(lrb_engine * e, double * ms, long long * groups, long long * kernels);
+/* bytes the engine actually moved over PCIe since the last lrb_profile_reset: input frames (host entry points) and read-back */
+LRB_API void lrb_profile_read_bytes(lrb_engine * e, long long * h2d_bytes, long long * d2h_bytes);
+/* FP32-pipe peaks of the engine's device, measured (csrc/ubench.cu): FFMA (2 flop per instruction) and FMA-free alternating
+ * FMUL / FADD (1 flop per instruction — the ceiling for this library's bit-exact, contraction-free arithmetic), in TFLOP/s.
+ * The scoring kernel's roofline fraction is reported against these. */
+LRB_API int lrb_ubench_fp32(lrb_engine * e, double * tflops_ffma, double * tflops_mul_add);
 
 /* One uniform-stream sample run, for the sampler known-answer tests: `count` 2-subsets of [0,n) from the start of
  * the stream; returns the number of draws consumed (or negative on error). pairs: host int32 [count*2]. */

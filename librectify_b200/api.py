@@ -72,6 +72,13 @@ def load_library(path: str | None = None):
         getattr(lib, name).argtypes = [vp, vp, ip, ip, ip, ll, ll, fp, vp, vp, ip]
     for name in ("lrb_rectify_device", "lrb_rectify_host"):
         getattr(lib, name).argtypes = [vp, vp, ip, ip, ip, ll, ll, fp, vp, ip, vp, vp]
+    lib.lrb_pool_create.argtypes = [vp, ip, ip, ip, C.POINTER(vp)]
+    lib.lrb_pool_destroy.argtypes = [vp]; lib.lrb_pool_destroy.restype = None
+    lib.lrb_pool_engines.argtypes = [vp]
+    lib.lrb_pool_engine.argtypes = [vp, ip]; lib.lrb_pool_engine.restype = vp
+    lib.lrb_pool_rectify_host.argtypes = [vp, vp, ip, ip, ip, ll, ll, fp, vp, ip, vp, vp, ip]
+    lib.lrb_pool_rectify_host_u8.argtypes = [vp, vp, ip, ip, ip, ip, ll, ll, fp, vp, ip, vp, vp, ip]
+    lib.lrb_pool_rectify_device.argtypes = [vp, vp, vp, ip, ip, ll, ll, fp, vp, ip, vp, vp, ip]
     lib.lrb_compute_transform.argtypes = [vp, ip, ip, ip, vp, vp]; lib.lrb_compute_transform.restype = None
     lib.lrb_compute_transform_from_vp.argtypes = [ip, ip, vp, vp, vp]; lib.lrb_compute_transform_from_vp.restype = None
     lib.lrb_fit_vanishing_point.argtypes = [vp, ip, ip, vp]; lib.lrb_fit_vanishing_point.restype = None
@@ -86,6 +93,8 @@ def load_library(path: str | None = None):
     lib.lrb_profile_enable.argtypes = [vp, ip]; lib.lrb_profile_enable.restype = None
     lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None
     lib.lrb_profile_read.argtypes = [vp, vp, vp, vp]; lib.lrb_profile_read.restype = None
+    lib.lrb_profile_read_bytes.argtypes = [vp, vp, vp]; lib.lrb_profile_read_bytes.restype = None
+    lib.lrb_ubench_fp32.argtypes = [vp, vp, vp]
     lib.lrb_sort_replay.argtypes = [vp, vp, ip, ip, vp]; lib.lrb_sort_replay.restype = ll
     lib.lrb_sample_pairs.argtypes = [vp, ip, ip, vp]; lib.lrb_sample_pairs.restype = ll
     lib.lrb_sample_pairs_parallel.argtypes = [vp, ip, ip, vp]; lib.lrb_sample_pairs_parallel.restype = ll
@@ -187,12 +196,16 @@ def tform_vec(t) -> np.ndarray:
 class Engine:
     """One CUDA device + stream + workspace of ``slots`` frames (include/librectify_b200.h)."""
 
-    def __init__(self, device: int = 0, slots: int = 1):
+    def __init__(self, device: int = 0, slots: int = 1, _borrowed=None):
         self.lib = load_library()
-        h = C.c_void_p()
-        rc = self.lib.lrb_engine_create(device, slots, C.byref(h))
-        if rc != 0:
-            raise LibrectifyError(_err(self.lib))
+        self.owned = _borrowed is None
+        if self.owned:
+            h = C.c_void_p()
+            rc = self.lib.lrb_engine_create(device, slots, C.byref(h))
+            if rc != 0:
+                raise LibrectifyError(_err(self.lib))
+        else:
+            h = C.c_void_p(_borrowed)              # an engine that belongs to a Pool
         self.h = h
         self.device = device
         self.slots = slots
@@ -200,7 +213,8 @@ class Engine:
 
     def close(self):
         if getattr(self, "h", None):
-            self.lib.lrb_engine_destroy(self.h)
+            if self.owned:
+                self.lib.lrb_engine_destroy(self.h)
             self.h = None
 
     def __del__(self):
@@ -429,4 +443,85 @@ class Engine:
         ms = (C.c_double * len(TIMERS))()
         g, k = C.c_longlong(0), C.c_longlong(0)
         self.lib.lrb_profile_read(self.h, ms, C.byref(g), C.byref(k))
-        return dict(ms={name: ms[i] for i, name in enumerate(TIMERS)}, groups=g.value, kernels=k.value)
+        h2d, d2h = C.c_longlong(0), C.c_longlong(0)
+        self.lib.lrb_profile_read_bytes(self.h, C.byref(h2d), C.byref(d2h))
+        return dict(ms={name: ms[i] for i, name in enumerate(TIMERS)}, groups=g.value, kernels=k.value,
+                    h2d_bytes=h2d.value, d2h_bytes=d2h.value)
+
+    def ubench_fp32(self) -> dict:
+        """measured FP32-pipe peaks of this device in TFLOP/s: FFMA and FMA-free FMUL/FADD (csrc/ubench.cu)"""
+        a, b = C.c_double(0), C.c_double(0)
+        self._check(self.lib.lrb_ubench_fp32(self.h, C.byref(a), C.byref(b)))
+        return dict(ffma=a.value, mul_add=b.value)
+
+
+# ---- the multi-GPU batch entry ---------------------------------------------------------------------------------------------
+class Pool:
+    """lrb_pool_*: ``engines_per_device`` engines on each of ``devices``; a call shards its frames over devices and engines
+    (frame i of B -> device floor(i * G / B)), one host thread per engine inside the library, results gathered in order."""
+
+    def __init__(self, devices=(0,), engines_per_device: int = 4, slots: int = 32):
+        self.lib = load_library()
+        self.devices = [int(d) for d in devices]
+        self.engines_per_device = engines_per_device
+        self.slots = slots
+        dv = (C.c_int * len(self.devices))(*self.devices)
+        h = C.c_void_p()
+        if self.lib.lrb_pool_create(dv, len(self.devices), engines_per_device, slots, C.byref(h)) != 0:
+            raise LibrectifyError(_err(self.lib))
+        self.h = h
+        n = self.lib.lrb_pool_engines(self.h)
+        self.engines = [Engine(self.devices[i // engines_per_device], slots, _borrowed=self.lib.lrb_pool_engine(self.h, i)) for i in range(n)]
+
+    def close(self):
+        if getattr(self, "h", None):
+            for e in self.engines:
+                e.close()
+            self.lib.lrb_pool_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise LibrectifyError(_err(self.lib))
+
+    def rectify_host(self, frames: np.ndarray, min_length: float, cfg: np.ndarray | None = None, passes: int = 1):
+        """frames: float32 [n,h,w] or uint8 [n,h,w] / [n,h,w,3] in host memory. Returns (transforms[n], info[n])."""
+        cfg = make_config() if cfg is None else np.ascontiguousarray(cfg, CFG_DTYPE)
+        if frames.dtype == np.uint8:
+            ptr, n, h, w, ch, pitch, fs, _, keep = Engine._frames_args_u8(frames)
+        else:
+            ptr, n, h, w, pitch, fs, _, keep = Engine._frames_args(frames); ch = 0
+        tf = np.zeros(n, TF_DTYPE); info = np.zeros(n, INFO_DTYPE)
+        if ch:
+            self._check(self.lib.lrb_pool_rectify_host_u8(self.h, ptr, n, w, h, ch, pitch, fs, C.c_float(min_length), cfg.ctypes.data, len(cfg),
+                                                          tf.ctypes.data, info.ctypes.data, passes))
+        else:
+            self._check(self.lib.lrb_pool_rectify_host(self.h, ptr, n, w, h, pitch, fs, C.c_float(min_length), cfg.ctypes.data, len(cfg),
+                                                       tf.ctypes.data, info.ctypes.data, passes))
+        return tf, info
+
+    def rectify_device(self, shards, min_length: float, cfg: np.ndarray | None = None, passes: int = 1):
+        """shards: one torch CUDA tensor [n_d,h,w] per pool device (resident on that device), or a single tensor for a
+        one-device pool. Returns (transforms, info) in shard order."""
+        if not isinstance(shards, (list, tuple)):
+            shards = [shards]
+        assert len(shards) == len(self.devices)
+        cfg = make_config() if cfg is None else np.ascontiguousarray(cfg, CFG_DTYPE)
+        args = [Engine._frames_args(t) if t is not None and t.shape[0] > 0 else None for t in shards]
+        first = next(a for a in args if a is not None)
+        _, _, h, w, pitch, fs, _, _ = first
+        ptrs = (C.c_void_p * len(shards))(*[a[0] if a else None for a in args])
+        counts = (C.c_int * len(shards))(*[a[1] if a else 0 for a in args])
+        for a in args:
+            assert a is None or (a[6] and a[2:6] == first[2:6]), "all shards: CUDA tensors of one frame size and layout"
+        n = sum(counts)
+        tf = np.zeros(n, TF_DTYPE); info = np.zeros(n, INFO_DTYPE)
+        self._check(self.lib.lrb_pool_rectify_device(self.h, ptrs, counts, w, h, pitch, fs, C.c_float(min_length), cfg.ctypes.data, len(cfg),
+                                                     tf.ctypes.data, info.ctypes.data, passes))
+        return tf, info

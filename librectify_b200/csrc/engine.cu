@@ -16,8 +16,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
+#include <functional>
 #include <vector>
 
 #include "../../include/librectify_b200.h"
@@ -110,11 +113,13 @@ struct lrb_engine {
     bool refine = false;               // run the `refine` merge post-process (reference interface.cpp:56-59)
     int seed_div = 8;                  // seed capacity = pixels / seed_div; grown to 1 the first time a frame needs it
     // uniform stream
+    std::shared_ptr<void> shared_stream;         // keeps the per-device copy of the uniform stream alive (see ensure_stream)
     unsigned * stream = nullptr; unsigned long long stream_len = 0; unsigned seed = 0;
     // bookkeeping of the last group
     int last_n = 0; std::vector<int> last_rounds, last_fallback;
     // profiling
     bool prof = false; cudaEvent_t ev[LRB_T_COUNT + 1] = {}; double ms[LRB_T_COUNT] = {}; long long groups = 0, kernels = 0;
+    long long h2d_bytes = 0, d2h_bytes = 0;      // bytes this engine actually moved over PCIe (input frames / read-back), since the last reset
 };
 
 namespace {
@@ -126,15 +131,40 @@ template <class T> T * carve(char *& p, size_t n)
     return r;
 }
 
+// The sampler's uniform stream depends on the seed only, so the engines of one device share ONE copy (128 MB at the default
+// length, ~28 ms to generate): a registry of weak references per (device, seed); an engine that needs a longer stream
+// generates a new one and the registry hands that to everybody who asks later.
+struct SharedStream {
+    unsigned * data = nullptr; unsigned long long len = 0; unsigned seed = 0; int device = 0;
+    ~SharedStream() { if (data) { int cur = 0; cudaGetDevice(&cur); cudaSetDevice(device); cudaFree(data); cudaSetDevice(cur); } }
+};
+std::mutex g_stream_mu;
+std::vector<std::weak_ptr<SharedStream>> g_streams;
+
 int ensure_stream(lrb_engine * e, unsigned long long need)
 {
     if (e->stream && e->stream_len >= need && e->seed == g_seed) return 0;
-    unsigned long long len = std::max<unsigned long long>(need, e->seed == g_seed ? e->stream_len : 0);
-    if (e->stream) { CK(cudaStreamSynchronize(e->st)); CK(cudaFree(e->stream)); e->stream = nullptr; }
-    CK(cudaMalloc(&e->stream, len * sizeof(unsigned)));
-    e->stream_len = len; e->seed = g_seed;
-    launch_mt_stream(e->seed, e->stream, len, e->st);
-    CK(cudaGetLastError());
+    std::lock_guard<std::mutex> lk(g_stream_mu);
+    std::shared_ptr<SharedStream> found;
+    for (auto it = g_streams.begin(); it != g_streams.end();) {
+        std::shared_ptr<SharedStream> s = it->lock();
+        if (!s) { it = g_streams.erase(it); continue; }
+        if (s->device == e->device && s->seed == g_seed && s->len >= need && (!found || s->len > found->len)) found = s;
+        ++it;
+    }
+    if (!found) {
+        found = std::make_shared<SharedStream>();
+        found->device = e->device; found->seed = g_seed; found->len = need;
+        CK(cudaMalloc(&found->data, need * sizeof(unsigned)));
+        launch_mt_stream(found->seed, found->data, need, e->st);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(e->st));          // complete before any other engine's stream may read it
+        e->kernels++;
+        g_streams.push_back(found);
+    }
+    if (e->stream) CK(cudaStreamSynchronize(e->st));   // kernels still reading the old copy
+    e->shared_stream = found;
+    e->stream = found->data; e->stream_len = found->len; e->seed = found->seed;
     return 0;
 }
 
@@ -253,6 +283,7 @@ int readback(lrb_engine * e, int n, Tick & tk)
     CK(cudaMemcpy2DAsync(e->h_lines, sizeof(SegRec) * kLinesHead, e->L.seg, sizeof(SegRec) * (size_t)e->L.cap,
                          sizeof(SegRec) * head, n, cudaMemcpyDeviceToHost, e->st));
     tk.end();
+    e->d2h_bytes += (long long)(sizeof(FrameCtrl) + sizeof(SegRec) * head) * n;
     CK(cudaStreamSynchronize(e->st));
     return 0;
 }
@@ -279,6 +310,7 @@ int copy_host_u8(lrb_engine * e, const unsigned char * src, int n, int w, int h,
     const size_t row = (size_t)w * ch;
     for (int i = 0; i < n; ++i)
         CK(cudaMemcpy2DAsync(e->u8_stage + (size_t)i * row * h, row, src + (long long)i * fstride, (size_t)pitch, row, h, cudaMemcpyHostToDevice, st));
+    e->h2d_bytes += (long long)(row * h) * n;
     return 0;
 }
 
@@ -286,6 +318,7 @@ int copy_host_frames(lrb_engine * e, const float * frames, int n, int w, int h, 
 {
     // dense batch (rows and frames back to back, and the workspace rows need no padding): the whole group is one contiguous
     // block -> ONE plain async copy instead of one 2-D copy per frame (a 32-frame 1080p group is a single 265 MB transfer)
+    e->h2d_bytes += (long long)sizeof(float) * w * h * n;
     if (pitch == w && e->pitch == w && fstride == (long long)w * h && e->plane == (size_t)w * h) {
         CK(cudaMemcpyAsync(e->ws_img, frames, sizeof(float) * (size_t)w * h * n, cudaMemcpyHostToDevice, st));
         return 0;
@@ -513,3 +546,4 @@ int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, i
 } // namespace
 
 #include "engine_api.inc"
+#include "pool_api.inc"

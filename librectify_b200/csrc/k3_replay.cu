@@ -25,10 +25,14 @@
 // (checked against std::sort on millions of elements with heavy ties, including the heap-sort branch: tests/test_sort_replay_gpu.py
 // drives this kernel through lrb_sort_replay against the oracle's std::sort.)
 //
-// Work distribution: one CTA per frame, warps pull ranges from a work list; a warp partitions its range with ballots
-// (three passes over the range: left stoppers, right stoppers, exchanges), pushes the right part and continues with the
-// left one, like the recursion it replays.  Keys are the dense ranks K3 computed (ties share a key; a SMALLER key is a
-// LARGER magnitude), the payload is the K3 rank (magnitude desc, raster asc) with the tied flag in bit 31.
+// Work distribution: one CTA (32 warps) per frame, two phases.
+//   Phase 1, ranges longer than kSmall: level by level, all ranges of a level at once (they are disjoint).  Every warp owns a
+//     contiguous slice of every range: count its stoppers, scan the 32 counts, write the stopper positions, then the whole
+//     CTA performs the exchanges.  A level costs a fixed number of barriers and memory round trips, whatever its ranges.
+//   Phase 2, ranges of at most kSmall elements: one warp per range, the range staged in shared memory; the warp follows the
+//     recursion below it on its own stack and writes the range back.
+// Keys are the dense ranks K3 computed (ties share a key; a SMALLER key is a LARGER magnitude), the payload is the K3 rank
+// (magnitude desc, raster asc) with the tied flag in bit 31.
 #include <climits>
 #include "common.cuh"
 #include "kernels.h"
@@ -72,52 +76,52 @@ __device__ void rp_heap_sort(uint2 * first, int len)
     while (last > 1) { --last; const uint2 v = first[last]; first[last] = first[0]; rp_adjust_heap(first, 0, last, v); }
 }
 
-// One __unguarded_partition_pivot of [f, l) by one warp.  Lp / Rp: scratch, only entries f+1 .. l-1 are used (so warps
-// working on disjoint ranges never meet).  Returns the cut; tied_left = tied elements in [f, cut) afterwards.
-__device__ int rp_partition(uint2 * a, int * Lp, int * Rp, int f, int l, int tied_total, int & tied_left)
+// __move_median_to_first(first, first + 1, mid, last - 1): index of the median of the three
+__device__ __forceinline__ int rp_median3(const uint2 * a, int f, int l)
+{
+    const int ia = f + 1, ib = f + (l - f) / 2, ic = l - 1;
+    const unsigned ka = a[ia].x, kb = a[ib].x, kc = a[ic].x;
+    if (rp_before(ka, kb)) { if (rp_before(kb, kc)) return ib; if (rp_before(ka, kc)) return ic; return ia; }
+    if (rp_before(ka, kc)) return ia;
+    if (rp_before(kb, kc)) return ic;
+    return ib;
+}
+
+// One __unguarded_partition_pivot of [f, l) by one warp on a range in shared memory (phase 2).  Lp / Rp: 16-bit scratch of the
+// range.  Returns the cut; tied_left = tied elements in [f, cut) afterwards.
+__device__ int rp_partition_small(uint2 * a, unsigned short * Lp, unsigned short * Rp, int f, int l, int tied_total, int & tied_left)
 {
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
-    // __move_median_to_first(first, first + 1, mid, last - 1)
-    const int mid = f + (l - f) / 2;
-    const int ia = f + 1, ib = mid, ic = l - 1;
-    const unsigned ka = a[ia].x, kb = a[ib].x, kc = a[ic].x;
-    int m;
-    if (rp_before(ka, kb)) { if (rp_before(kb, kc)) m = ib; else if (rp_before(ka, kc)) m = ic; else m = ia; }
-    else if (rp_before(ka, kc)) m = ia;
-    else if (rp_before(kb, kc)) m = ic;
-    else m = ib;
+    const int m = rp_median3(a, f, l);
     __syncwarp();
     if (lane == 0) { const uint2 t = a[f]; a[f] = a[m]; a[m] = t; }
     __syncwarp();
     const unsigned pv = a[f].x;
-    // left stoppers, in scan order: !(x before pivot)
-    int cL = 0;
+    int cL = 0;                                                            // left stoppers, in scan order: !(x before pivot)
     for (int base = f + 1; base < l; base += 32) {
         const int i = base + lane;
         const bool fl = i < l && !rp_before(a[i].x, pv);
         const unsigned bal = __ballot_sync(0xffffffffu, fl);
-        if (fl) Lp[f + 1 + cL + __popc(bal & lt)] = i;
+        if (fl) Lp[cL + __popc(bal & lt)] = (unsigned short)i;
         cL += __popc(bal);
     }
-    // right stoppers, in scan order (from the right): !(pivot before x)
-    int cR = 0;
+    int cR = 0;                                                            // right stoppers, from the right: !(pivot before x)
     for (int base = l - 1; base > f; base -= 32) {
         const int i = base - lane;
         const bool fl = i > f && !rp_before(pv, a[i].x);
         const unsigned bal = __ballot_sync(0xffffffffu, fl);
-        if (fl) Rp[f + 1 + cR + __popc(bal & lt)] = i;
+        if (fl) Rp[cR + __popc(bal & lt)] = (unsigned short)i;
         cR += __popc(bal);
     }
     __syncwarp();
-    // exchanges: the k-th left stopper with the k-th right stopper while it lies left of it
     const int mn = min(cL, cR);
     int K = 0;
-    for (int kb0 = 0; kb0 < mn; kb0 += 32) {
+    for (int kb0 = 0; kb0 < mn; kb0 += 32) {                               // the k-th left stopper <-> the k-th right stopper while left of it
         const int k = kb0 + lane;
         bool sw = false;
         if (k < mn) {
-            const int lp = Lp[f + 1 + k], rp = Rp[f + 1 + k];
+            const int lp = Lp[k], rp = Rp[k];
             sw = lp < rp;
             if (sw) { const uint2 x = a[lp], y = a[rp]; a[lp] = y; a[rp] = x; }
         }
@@ -126,10 +130,7 @@ __device__ int rp_partition(uint2 * a, int * Lp, int * Rp, int f, int l, int tie
         if (bal != 0xffffffffu) break;
     }
     __syncwarp();
-    int cut;
-    if (K == 0) cut = Lp[f + 1];
-    else cut = min(K < cL ? Lp[f + 1 + K] : INT_MAX, Rp[f + 1 + K - 1]);
-    // tied elements on the smaller side
+    const int cut = (K == 0) ? (int)Lp[0] : min(K < cL ? (int)Lp[K] : INT_MAX, (int)Rp[K - 1]);
     const bool left_small = (cut - f) <= (l - cut);
     const int s0 = left_small ? f : cut, s1 = left_small ? cut : l;
     int cnt = 0;
@@ -140,10 +141,29 @@ __device__ int rp_partition(uint2 * a, int * Lp, int * Rp, int f, int l, int tie
     return cut;
 }
 
+constexpr int kSmall = 512;                   // ranges up to this size are finished by one warp in shared memory
+constexpr int kMaxSeg = 64;                   // ranges of one level processed together in phase 1
+constexpr int kWorkers = 8;                   // warps that take part in phase 2
+constexpr int kStack = 48;                    // >= 2 * log2(kSmall) + slack: pending right parts below one small range
+
+struct RpPhase1 {                             // shared memory of phase 1
+    int4 seg[kMaxSeg];                        // first, last, depth left, tied elements
+    unsigned piv[kMaxSeg];
+    int cntL[kMaxSeg][32], cntR[kMaxSeg][32]; // stoppers per warp slice -> exclusive prefix (L) / suffix (R)
+    int totL[kMaxSeg], totR[kMaxSeg], K[kMaxSeg], cut[kMaxSeg], tl[kMaxSeg];
+};
+struct RpPhase2 {                             // shared memory of phase 2 (one set per worker warp)
+    uint2 a[kWorkers][kSmall];
+    unsigned short Lp[kWorkers][kSmall], Rp[kWorkers][kSmall];
+};
+union RpShared { RpPhase1 p1; RpPhase2 p2; };
+
 __global__ void __launch_bounds__(RP_THREADS)
 k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup)
 {
-    __shared__ int q_head, q_tail, q_lock, pending, steps;
+    extern __shared__ __align__(16) unsigned char rp_smem_raw[];
+    RpShared & sh = *reinterpret_cast<RpShared *>(rp_smem_raw);
+    __shared__ int n_cur, n_next, n_small, small_head, steps;
     const int slot = blockIdx.x;
     FrameCtrl & C = ctrl[slot];
     const int n = min(C.n_seeds, S.cap);
@@ -151,75 +171,208 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
     if (n_tied < 2 || n <= kSortThreshold || C.seed_overflow) return;      // no ties, or a plain (stable) insertion sort: K3's order is final
     const size_t so = (size_t)slot * S.cap;
     uint2 * a = S.rp_el + so;
-    int4 * q = S.rp_q + so;
+    // work lists in global memory: two level lists (ping-pong) and the list of small ranges; every listed range holds more than
+    // kSortThreshold elements and ranges of one list are disjoint, so cap / 3 entries each are ample
+    int4 * qbase = S.rp_q + so;
+    const int qcap = S.cap / 3;
+    int4 * qa = qbase; int4 * qb = qbase + qcap; int4 * qs = qbase + 2 * (size_t)qcap;
     int * Lp = reinterpret_cast<int *>(S.us_mag + so);                     // free after k_seed_scatter
     int * Rp = reinterpret_cast<int *>(S.us_idx + so);
-    const int lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    if (tid == 0) {
         int lg = 0; while ((2 << lg) <= n) ++lg;                           // std::__lg(n)
-        q[0] = make_int4(0, n, depth_override >= 0 ? depth_override : 2 * lg, n_tied);
-        q_head = 0; q_tail = 1; q_lock = 0; pending = 1; steps = 0;
+        const int4 root = make_int4(0, n, depth_override >= 0 ? depth_override : 2 * lg, n_tied);
+        n_cur = 0; n_next = 0; n_small = 0; small_head = 0; steps = 0;
+        if (n > kSmall) { qa[0] = root; n_cur = 1; } else { qs[0] = root; n_small = 1; }
     }
     __syncthreads();
-    volatile int * vhead = &q_head; volatile int * vtail = &q_tail; volatile int * vpend = &pending;
+
+    // ---- phase 1: ranges longer than kSmall, level by level ---------------------------------------------------------------
+    RpPhase1 & A = sh.p1;
     while (true) {
-        int item = -1;
-        if (lane == 0) {
-            while (true) {
-                if (*vpend == 0) { item = -2; break; }
-                if (*vhead < *vtail) {
-                    while (atomicCAS(&q_lock, 0, 1) != 0) { }
-                    __threadfence_block();
-                    if (*vhead < *vtail) { item = *vhead; *vhead = item + 1; }
-                    __threadfence_block();
-                    atomicExch(&q_lock, 0);
-                    if (item >= 0) break;
-                } else __nanosleep(200);
+        const int na = n_cur;
+        if (na == 0) break;
+        for (int b0 = 0; b0 < na; b0 += kMaxSeg) {
+            const int ns = min(kMaxSeg, na - b0);
+            __syncthreads();
+            // (0) depth limit / pivot
+            if (tid < ns) {
+                int4 g = qa[b0 + tid];
+                if (g.z == 0) { rp_heap_sort(a + g.x, g.y - g.x); g.y = g.x; }          // sorted: nothing left to do in this range
+                else { const int m = rp_median3(a, g.x, g.y); const uint2 t = a[g.x]; a[g.x] = a[m]; a[m] = t; A.piv[tid] = a[g.x].x; }
+                A.seg[tid] = g;
             }
-        }
-        item = __shfl_sync(0xffffffffu, item, 0);
-        if (item == -2) break;
-        const int4 seg = __ldcg(&q[item]);
-        int f = seg.x, l = seg.y, d = seg.z, t = seg.w, my_steps = 0;
-        while (l - f > kSortThreshold && t >= 2) {
-            if (d == 0) {                                                  // std::__partial_sort(first, last, last): the range ends up sorted
-                if (lane == 0) rp_heap_sort(a + f, l - f);
-                __syncwarp();
-                break;
+            __syncthreads();
+            // (1) stoppers per warp slice
+            for (int s = 0; s < ns; ++s) {
+                const int f = A.seg[s].x, l = A.seg[s].y;
+                if (l <= f) continue;
+                const unsigned pv = A.piv[s];
+                const int c = ((l - f - 1 + 31) / 32 + 31) / 32 * 32;                    // slice length: a multiple of 32
+                const int i0 = f + 1 + warp * c, i1 = min(l, i0 + c);
+                int cl = 0, cr = 0;
+#pragma unroll 4
+                for (int i = i0 + lane; i < i1; i += 32) { const unsigned k = a[i].x; cl += !rp_before(k, pv); cr += !rp_before(pv, k); }
+#pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1) { cl += __shfl_xor_sync(0xffffffffu, cl, sft); cr += __shfl_xor_sync(0xffffffffu, cr, sft); }
+                if (lane == 0) { A.cntL[s][warp] = cl; A.cntR[s][warp] = cr; }
             }
-            --d;
-            int tl;
-            const int cut = rp_partition(a, Lp, Rp, f, l, t, tl);
-            ++my_steps;
-            const int tr = t - tl;
-            if (l - cut > kSortThreshold && tr >= 2) {                     // __introsort_loop(cut, last, depth_limit)
-                if (lane == 0) {
-                    while (atomicCAS(&q_lock, 0, 1) != 0) { }
-                    __threadfence_block();
-                    const int at = *vtail;
-                    q[at] = make_int4(cut, l, d, tr);
-                    __threadfence_block();
-                    *vtail = at + 1; atomicAdd(&pending, 1);
-                    __threadfence_block();
-                    atomicExch(&q_lock, 0);
+            __syncthreads();
+            // (2) prefix of the left stoppers, suffix of the right stoppers over the 32 slices
+            for (int s = warp; s < ns; s += 32) {
+                const int cl = A.cntL[s][lane], cr = A.cntR[s][lane];
+                int il = cl, ir = cr;
+#pragma unroll
+                for (int sft = 1; sft < 32; sft <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, il, sft); if (lane >= sft) il += v;
+                    const int u = __shfl_down_sync(0xffffffffu, ir, sft); if (lane + sft < 32) ir += u;
                 }
-                __syncwarp();
+                A.cntL[s][lane] = il - cl; A.cntR[s][lane] = ir - cr;
+                if (lane == 31) A.totL[s] = il;
+                if (lane == 0) { A.totR[s] = ir; A.K[s] = 0; }
             }
-            l = cut; t = tl;                                               // last = cut
+            __syncthreads();
+            // (3) stopper positions, in scan order
+            for (int s = 0; s < ns; ++s) {
+                const int f = A.seg[s].x, l = A.seg[s].y;
+                if (l <= f) continue;
+                const unsigned pv = A.piv[s];
+                const int c = ((l - f - 1 + 31) / 32 + 31) / 32 * 32;
+                const int i0 = f + 1 + warp * c, i1 = min(l, i0 + c);
+                int bl = A.cntL[s][warp];
+                // right stoppers of this slice that lie right of element i = (all of the slice) - (those up to and including i)
+                const int slice_r = (warp == 0 ? A.totR[s] : A.cntR[s][warp - 1]) - A.cntR[s][warp];
+                int br = A.cntR[s][warp] + slice_r;                                      // index of a right stopper = br - (right stoppers of the slice up to and including it)
+                for (int base = i0; base < i1; base += 32) {
+                    const int i = base + lane;
+                    const unsigned k = i < i1 ? a[i].x : 0u;
+                    const bool fL = i < i1 && !rp_before(k, pv), fR = i < i1 && !rp_before(pv, k);
+                    const unsigned bL = __ballot_sync(0xffffffffu, fL), bR = __ballot_sync(0xffffffffu, fR);
+                    if (fL) Lp[f + 1 + bl + __popc(bL & lt)] = i;
+                    if (fR) Rp[f + 1 + br - 1 - __popc(bR & lt)] = i;
+                    bl += __popc(bL); br -= __popc(bR);
+                }
+            }
+            __syncthreads();
+            // (4) exchanges: L[k] <-> R[k] while L[k] < R[k] (true for a prefix of k); K = length of that prefix
+            for (int s = 0; s < ns; ++s) {
+                const int f = A.seg[s].x, l = A.seg[s].y;
+                if (l <= f) continue;
+                const int mn = min(A.totL[s], A.totR[s]);
+                for (int k = tid; k < mn; k += RP_THREADS) {
+                    const int lp = Lp[f + 1 + k], rp = Rp[f + 1 + k];
+                    const bool sw = lp < rp;
+                    if (sw) {
+                        const uint2 x = a[lp], y = a[rp]; a[lp] = y; a[rp] = x;
+                        const bool nxt = (k + 1 < mn) && (Lp[f + 2 + k] < Rp[f + 2 + k]);
+                        if (!nxt) A.K[s] = k + 1;
+                    }
+                }
+            }
+            __syncthreads();
+            // (5) the cut
+            if (tid < ns) {
+                const int f = A.seg[tid].x, l = A.seg[tid].y;
+                if (l > f) {
+                    const int K = A.K[tid];
+                    A.cut[tid] = (K == 0) ? Lp[f + 1] : min(K < A.totL[tid] ? Lp[f + 1 + K] : INT_MAX, Rp[f + K]);
+                }
+                A.tl[tid] = 0;
+            }
+            __syncthreads();
+            // (6) tied elements on the smaller side
+            for (int s = 0; s < ns; ++s) {
+                const int f = A.seg[s].x, l = A.seg[s].y;
+                if (l <= f) continue;
+                const int cut = A.cut[s];
+                const bool left_small = (cut - f) <= (l - cut);
+                const int s0 = left_small ? f : cut, s1 = left_small ? cut : l;
+                int cnt = 0;
+                for (int i = s0 + tid; i < s1; i += RP_THREADS) cnt += (a[i].y & kTiedBit) ? 1 : 0;
+                if (__any_sync(0xffffffffu, cnt != 0)) {
+#pragma unroll
+                    for (int sft = 16; sft > 0; sft >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, sft);
+                    if (lane == 0 && cnt) atomicAdd(&A.tl[s], cnt);
+                }
+            }
+            __syncthreads();
+            // (7) children: [f, cut) continues the loop, [cut, l) is the recursive call; both with the decremented depth limit
+            if (tid < ns) {
+                const int4 g = A.seg[tid];
+                if (g.y > g.x) {
+                    const int cut = A.cut[tid];
+                    const bool left_small = (cut - g.x) <= (g.y - cut);
+                    const int tl = left_small ? A.tl[tid] : g.w - A.tl[tid];
+                    const int4 kid[2] = {make_int4(g.x, cut, g.z - 1, tl), make_int4(cut, g.y, g.z - 1, g.w - tl)};
+                    for (int c = 0; c < 2; ++c) {
+                        const int len = kid[c].y - kid[c].x;
+                        if (len <= kSortThreshold || kid[c].w < 2) continue;
+                        if (len > kSmall) qb[atomicAdd(&n_next, 1)] = kid[c];
+                        else qs[atomicAdd(&n_small, 1)] = kid[c];
+                    }
+                    atomicAdd(&steps, 1);
+                }
+            }
         }
-        __threadfence_block();
-        if (lane == 0) { atomicSub(&pending, 1); atomicAdd(&steps, my_steps); }
+        __syncthreads();
+        if (tid == 0) { n_cur = n_next; n_next = 0; }
+        int4 * t = qa; qa = qb; qb = t;
+        __syncthreads();
     }
     __syncthreads();
-    if (threadIdx.x == 0) C.replay_steps = steps;
+
+    // ---- phase 2: small ranges, one warp each, in shared memory ----------------------------------------------------------
+    if (warp < kWorkers) {
+        RpPhase2 & B = sh.p2;
+        uint2 * sa = B.a[warp]; unsigned short * sL = B.Lp[warp]; unsigned short * sR = B.Rp[warp];
+        int4 stack[kStack];
+        int my_steps = 0;
+        const int nsm = n_small;
+        while (true) {
+            int item = 0;
+            if (lane == 0) item = atomicAdd(&small_head, 1);
+            item = __shfl_sync(0xffffffffu, item, 0);
+            if (item >= nsm) break;
+            const int4 g = qs[item];
+            const int len = g.y - g.x;
+            for (int i = lane; i < len; i += 32) sa[i] = a[g.x + i];
+            __syncwarp();
+            int sp = 0;
+            stack[sp++] = make_int4(0, len, g.z, g.w);
+            while (sp > 0) {
+                const int4 r = stack[--sp];
+                int f = r.x, l = r.y, d = r.z, t = r.w;
+                while (l - f > kSortThreshold && t >= 2) {
+                    if (d == 0) {                                          // std::__partial_sort(first, last, last): the range ends up sorted
+                        if (lane == 0) rp_heap_sort(sa + f, l - f);
+                        __syncwarp();
+                        break;
+                    }
+                    --d;
+                    int tl;
+                    const int cut = rp_partition_small(sa, sL, sR, f, l, t, tl);
+                    ++my_steps;
+                    if (l - cut > kSortThreshold && t - tl >= 2 && sp < kStack) stack[sp++] = make_int4(cut, l, d, t - tl);   // __introsort_loop(cut, last, depth_limit)
+                    l = cut; t = tl;                                       // last = cut
+                }
+            }
+            __syncwarp();
+            for (int i = lane; i < len; i += 32) a[g.x + i] = sa[i];
+            __syncwarp();
+        }
+        if (lane == 0 && my_steps) atomicAdd(&steps, my_steps);
+    }
+    __syncthreads();
+    if (tid == 0) C.replay_steps = steps;
     if (!fixup) return;
     // ---- final order: stable by key of the arrangement above.  Only tied peaks move, inside their group's rank range. ----
     // (1) position of every rank
-    for (int p = threadIdx.x; p < n; p += RP_THREADS) Lp[a[p].y & ~kTiedBit] = p;
+    for (int p = tid; p < n; p += RP_THREADS) Lp[a[p].y & ~kTiedBit] = p;
     __syncthreads();
     // (2) final rank of a tied peak = first rank of its group + members of the group left of it; remember its pixel
     unsigned * sidx = S.idx + so;
-    for (int p = threadIdx.x; p < n; p += RP_THREADS) {
+    for (int p = tid; p < n; p += RP_THREADS) {
         const uint2 el = a[p];
         if (!(el.y & kTiedBit)) continue;
         const int rank = (int)(el.y & ~kTiedBit);
@@ -232,14 +385,14 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
         Rp[rank] = (int)el.x + before;
     }
     __syncthreads();
-    for (int p = threadIdx.x; p < n; p += RP_THREADS) {                    // Lp is free again: park the pixel of every tied rank
+    for (int p = tid; p < n; p += RP_THREADS) {                            // Lp is free again: park the pixel of every tied rank
         const uint2 el = a[p];
         if (el.y & kTiedBit) { const int rank = (int)(el.y & ~kTiedBit); Lp[rank] = (int)sidx[rank]; }
     }
     __syncthreads();
     // (3) move the per-seed records (pixel, bin, flood threshold; the other per-seed arrays still hold their initial values)
     const size_t pbase = (size_t)slot * P.stride;
-    for (int p = threadIdx.x; p < n; p += RP_THREADS) {
+    for (int p = tid; p < n; p += RP_THREADS) {
         const uint2 el = a[p];
         if (!(el.y & kTiedBit)) continue;
         const int rank = (int)(el.y & ~kTiedBit), fr = Rp[rank];
@@ -258,8 +411,10 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
 
 void launch_seed_replay(const Planes & P, const Seeds & S, FrameCtrl * ctrl, int n_slots, int depth_override, bool fixup, cudaStream_t st)
 {
+    static PerDeviceOnce once;
+    once.run([] { cudaFuncSetAttribute(k_seed_replay, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RpShared)); });
     LRB_CARVEOUT(k_seed_replay);
-    k_seed_replay<<<n_slots, RP_THREADS, 0, st>>>(P, S, ctrl, depth_override, fixup ? 1 : 0);
+    k_seed_replay<<<n_slots, RP_THREADS, sizeof(RpShared), st>>>(P, S, ctrl, depth_override, fixup ? 1 : 0);
 }
 
 } // namespace lrb

@@ -47,6 +47,8 @@ void launch_ingest_u8(const unsigned char * src, long long src_pitch, long long 
                       int dst_pitch, size_t dst_stride, int w, int h, int n_slots, cudaStream_t st);
 void launch_fill_u32(unsigned * p, size_t n, unsigned v, cudaStream_t st);
 void launch_mt_raw(unsigned seed, unsigned * out, unsigned long long n, cudaStream_t st);
+// ubench.cu: FP32-pipe peaks (mode 0: FFMA, 1: alternating FMUL / FADD); out: blocks * 256 floats
+void launch_ubench_fp32(int mode, float * out, int blocks, int iters, cudaStream_t st);
 // k_hough.cu
 size_t hough_out_bytes();
 int hough_draws();

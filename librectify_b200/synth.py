@@ -26,38 +26,54 @@ def _homography(src: np.ndarray, dst: np.ndarray) -> np.ndarray:
     return np.append(h, 1.0).reshape(3, 3)
 
 
-def scene_canvas(seed: int, width: int, height: int, n_lines: int = 40, canvas_scale: float = 2.0):
-    """Draw the axis-aligned canvas and the frame<-canvas homography. Returns (canvas f32 [S,S], Hinv 3x3 f64, H 3x3)."""
+def scene_ops(seed: int, width: int, height: int, n_lines: int = 40, canvas_scale: float = 2.0):
+    """The scene as a list of fill operations (y0, y1, x0, x1, grey) on the S x S canvas, plus the homography.
+    Returns (S, ops, Hinv 3x3 f64, H 3x3, rng) — the rng is handed on for the noise seed (same draw order as ever)."""
     rng = np.random.default_rng(seed)
     S = int(canvas_scale * max(width, height))
-    canvas = np.full((S, S), 0.75, dtype=np.float32)
     L = n_lines
+    ops = []
     for _ in range(3 * L):
         w = int(rng.integers(S // 40, S // 6))
         h = int(rng.integers(S // 40, S // 6))
         x = int(rng.integers(0, S - w))
         y = int(rng.integers(0, S - h))
-        canvas[y:y + h, x:x + w] = np.float32(rng.uniform(0.1, 0.95))
+        ops.append((y, y + h, x, x + w, np.float32(rng.uniform(0.1, 0.95))))
     for _ in range(L):
         t = int(rng.integers(1, 5)); x = int(rng.integers(0, S - t))
-        canvas[:, x:x + t] = np.float32(rng.uniform(0.0, 1.0))
+        ops.append((0, S, x, x + t, np.float32(rng.uniform(0.0, 1.0))))
     for _ in range(L):
         t = int(rng.integers(1, 5)); y = int(rng.integers(0, S - t))
-        canvas[y:y + t, :] = np.float32(rng.uniform(0.0, 1.0))
+        ops.append((y, y + t, 0, S, np.float32(rng.uniform(0.0, 1.0))))
     src = np.array([[0, 0], [S, 0], [S, S], [0, S]], dtype=np.float64)
     dst = np.array([[0, 0], [width, 0], [width, height], [0, height]], dtype=np.float64)
     dst = dst + rng.uniform(-0.15, 0.15, size=(4, 2)) * np.array([width, height])
     H = _homography(src, dst)
-    return canvas, np.linalg.inv(H), H, rng
+    return S, ops, np.linalg.inv(H), H, rng
+
+
+def scene_canvas(seed: int, width: int, height: int, n_lines: int = 40, canvas_scale: float = 2.0):
+    """Draw the axis-aligned canvas and the frame<-canvas homography. Returns (canvas f32 [S,S], Hinv 3x3 f64, H 3x3)."""
+    S, ops, Hinv, H, rng = scene_ops(seed, width, height, n_lines, canvas_scale)
+    canvas = np.full((S, S), 0.75, dtype=np.float32)
+    for y0, y1, x0, x1, v in ops:
+        canvas[y0:y1, x0:x1] = v
+    return canvas, Hinv, H, rng
 
 
 def manhattan_frame(seed: int, width: int = 1920, height: int = 1080, n_lines: int = 40,
                     device: str | torch.device = "cpu", canvas_scale: float = 2.0) -> torch.Tensor:
     """One synthetic frame, float32 [height, width] on ``device``."""
-    canvas, Hinv, _, rng = scene_canvas(seed, width, height, n_lines, canvas_scale)
-    S = canvas.shape[0]
     dev = torch.device(device)
-    cv = torch.from_numpy(canvas).to(dev)
+    if dev.type == "cuda":      # same canvas, drawn on the device (the fills are exact float32 assignments): no 59 MB upload per frame
+        S, ops, Hinv, _, rng = scene_ops(seed, width, height, n_lines, canvas_scale)
+        cv = torch.full((S, S), 0.75, dtype=torch.float32, device=dev)
+        for y0, y1, x0, x1, v in ops:
+            cv[y0:y1, x0:x1] = float(v)
+    else:
+        canvas, Hinv, _, rng = scene_canvas(seed, width, height, n_lines, canvas_scale)
+        S = canvas.shape[0]
+        cv = torch.from_numpy(canvas)
     ys, xs = torch.meshgrid(torch.arange(height, device=dev, dtype=torch.float64) + 0.5,
                             torch.arange(width, device=dev, dtype=torch.float64) + 0.5, indexing="ij")
     Hi = torch.from_numpy(Hinv).to(dev)

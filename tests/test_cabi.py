@@ -131,3 +131,25 @@ def test_corner_solve_matches_oracle_on_perturbed_groups(oracle, golden):
         assert np.array_equal(a, b, equal_nan=True), trial
         for g in (-1, 0, 1, 2):
             assert np.array_equal(np.float32(api.fit_vanishing_point(s, g)), np.float32(oracle.fit_vanishing_point(s, g)), equal_nan=True)
+
+
+def test_cpp_program_links_against_the_drop_in(tmp_path):
+    """A C++ translation unit that includes include/librectify.h the way a user of the reference includes src/librectify.h
+    (reference src/test.cpp:1-43 does exactly this) compiles with g++, links against librectify_b200.so and prints the
+    reference program's four known answers.  Host-side functions only: no GPU needed."""
+    import shutil
+    import subprocess
+    cxx = shutil.which("g++")
+    assert cxx, "g++ is part of the image"
+    src = os.path.join(ROOT, "tests", "boundary", "dropin_kat.cpp")
+    exe = str(tmp_path / "dropin_kat")
+    libdir = os.path.dirname(api.LIB_PATH)
+    subprocess.check_call([cxx, "-std=c++14", "-O1", "-I", os.path.join(ROOT, "include"), src, "-o", exe,
+                           "-L", libdir, "-l:librectify_b200.so", "-Wl,-rpath," + libdir])
+    out = subprocess.run([exe], capture_output=True, text=True, check=True).stdout.splitlines()
+    assert out[0] == "vp1=[5,12.5,1]"
+    assert out[1] == "vp2=[1,0,0]"
+    assert out[2].startswith("vp3=[5,2.7578") and out[2].endswith(",1]")
+    assert out[3] == "Assigned to group 1"
+    assert out[4] == "size=10x5 strategies=2,2"                      # RECTIFY / RECTIFY defaults (reference src/librectify.h:137-150)
+    assert out[5] == "ideal=[0,0] [640,480]"                         # ideal points on both axes: the identity
