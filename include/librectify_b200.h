@@ -48,6 +48,8 @@ typedef struct lrb_frame_info {
     int n_solves;         /* vanishing-point structures estimated (<= 4) */
     int n_obs[4];         /* observations per solve: the scoring grid is 10^4 x n_obs[k] */
     float max_magnitude;
+    int floods_small;     /* tentative floods finished inside the sub-warp window (k_flood_small), all rounds */
+    int floods_escalated; /* tentative floods handed on to the full-tile path */
 } lrb_frame_info;
 
 typedef struct lrb_engine lrb_engine;
@@ -211,7 +213,9 @@ LRB_API long long lrb_stage_fetch(lrb_engine * e, int slot, int stage, void * ds
 
 /* ---- per-stage device timings (CUDA events on the engine's stream) ---------------------------------------------- */
 enum lrb_timer { LRB_T_INGEST = 0, LRB_T_GRAD, LRB_T_NMS, LRB_T_SEEDS, LRB_T_FLOOD, LRB_T_FIT, LRB_T_MODEL,
-                 LRB_T_RANSAC, LRB_T_READBACK, LRB_T_COUNT };
+                 LRB_T_RANSAC, LRB_T_READBACK,
+                 LRB_T_SCORE,      /* not a stage of its own: the k_score launches (scoring grid) inside LRB_T_RANSAC */
+                 LRB_T_COUNT };
 LRB_API void lrb_profile_enable(lrb_engine * e, int on);
 LRB_API void lrb_profile_reset(lrb_engine * e);
 /* ms[LRB_T_COUNT]: summed device milliseconds per stage; groups: launch groups timed; kernels: kernels launched */

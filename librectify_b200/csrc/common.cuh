@@ -85,6 +85,8 @@ struct FrameCtrl {
     int win_live, win_first, win_blocks;   // commit-kernel scratch (live seeds left in the window, lowest of them, blocks done)
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
     int queue[kMaxRounds + 1]; // queue[r]: next window position handed out in flood round r (warps take seeds dynamically, in priority order)
+    int floods_small, floods_esc;   // statistics over all rounds: floods finished in the sub-warp window / escalated
+    int esc_n, esc_q;          // floods of the current round that outgrew the sub-warp window (escalated to the full-tile path), next one handed out
     int fit_queue;             // next kept component handed out by the fit kernel
     int n_edges, n_merged, refine_overflow;   // `refine` post-process (k_refine.cu): collinearity edges, merged segments, edge list full
     // grouping state
@@ -131,6 +133,7 @@ struct Seeds {                  // per slot: s * cap
     unsigned * fail_epoch;
     int * size;
     int * list_head;                          // first pool chunk of the seed's tentative pixel list (this round)
+    int * esc;                                // ranks of this round's escalated floods (see k_flood_small)
     int * hist; int * start; int * cursor;    // kSeedBuckets each per slot
     // raster order of the peaks and the std::sort replay (k3_replay.cu): the reference sorts its peak list, which is in raster
     // order, with std::sort (reference src/filter.cpp:174-188) — unstable, so the order of exact-magnitude ties is whatever

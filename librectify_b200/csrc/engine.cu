@@ -118,7 +118,7 @@ struct lrb_engine {
     // bookkeeping of the last group
     int last_n = 0; std::vector<int> last_rounds, last_fallback;
     // profiling
-    bool prof = false; cudaEvent_t ev[LRB_T_COUNT + 1] = {}; double ms[LRB_T_COUNT] = {}; long long groups = 0, kernels = 0;
+    bool prof = false; cudaEvent_t ev[LRB_T_COUNT + 1] = {}; cudaEvent_t ev_score[2 * kMaxModels] = {}; double ms[LRB_T_COUNT] = {}; long long groups = 0, kernels = 0;
     long long h2d_bytes = 0, d2h_bytes = 0;      // bytes this engine actually moved over PCIe (input frames / read-back), since the last reset
 };
 
@@ -198,7 +198,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
         e->S.idx = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.thr = carve<float>(p, (size_t)cap_seeds * G);
         e->S.bin = carve<uint8_t>(p, (size_t)cap_seeds * G); e->S.status = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.fail_epoch = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.size = carve<int>(p, (size_t)cap_seeds * G);
-        e->S.list_head = carve<int>(p, (size_t)cap_seeds * G);
+        e->S.list_head = carve<int>(p, (size_t)cap_seeds * G); e->S.esc = carve<int>(p, (size_t)cap_seeds * G);
         e->S.hist = carve<int>(p, (size_t)kSeedBuckets * G); e->S.start = carve<int>(p, (size_t)kSeedBuckets * G);
         e->S.cursor = carve<int>(p, (size_t)kSeedBuckets * G);
         e->S.rowhist = carve<int>(p, (size_t)h * G); e->S.rowstart = carve<int>(p, (size_t)h * G); e->S.rowcursor = carve<int>(p, (size_t)h * G);
@@ -271,7 +271,7 @@ void enqueue_tail(lrb_engine * e, int n, float min_length, int rounds_total, Tic
     if (e->refine) e->kernels += launch_refine(e->K, e->ctrl, n, e->st);
     launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds_total, e->refine, e->st);
     tk.at(LRB_T_RANSAC);
-    launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st);
+    launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st, e->prof ? e->ev_score : nullptr);
     e->kernels += 2 + 1 + 6 * kMaxModels + 1;
 }
 
@@ -296,6 +296,10 @@ void collect_profile(lrb_engine * e, const std::vector<int> & order)
         cudaEvent_t a = e->ev[order[i]], b = (i + 1 < order.size()) ? e->ev[order[i + 1]] : e->ev[LRB_T_COUNT];
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, a, b) == cudaSuccess) e->ms[order[i]] += ms;
+    }
+    for (int k = 0; k < kMaxModels; ++k) {           // the scoring grid alone (a sub-interval of the RANSAC stage)
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e->ev_score[2 * k], e->ev_score[2 * k + 1]) == cudaSuccess) e->ms[LRB_T_SCORE] += ms;
     }
 }
 
@@ -433,7 +437,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         stage(LRB_T_FIT); launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds, e->st);
         stage(LRB_T_MODEL); if (e->refine) e->kernels += launch_refine(e->K, e->ctrl, n, e->st);
         launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds, e->refine, e->st);
-        stage(LRB_T_RANSAC); launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st);
+        stage(LRB_T_RANSAC); launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st, e->prof ? e->ev_score : nullptr);
         stage(LRB_T_READBACK);
         order.resize(order.size() - 4);
         if (stage_err != cudaSuccess) return fail(-2, "debug sync: a stage failed (see stderr): %s", cudaGetErrorString(stage_err));
@@ -504,6 +508,7 @@ void fill_info(const lrb_engine * e, int i, lrb_frame_info * out)
     out->flood_rounds = C.rounds_run; out->flood_fallback = e->last_fallback[i]; out->n_solves = C.n_solves;
     for (int k = 0; k < 4; ++k) out->n_obs[k] = k < C.n_solves ? C.n_obs[k] : 0;
     unsigned g = C.gmax_bits; float f; memcpy(&f, &g, 4); out->max_magnitude = f;
+    out->floods_small = C.floods_small; out->floods_escalated = C.floods_esc;
 }
 
 int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, int w, int h, long long pitch,

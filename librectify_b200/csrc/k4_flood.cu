@@ -21,6 +21,7 @@
 // mask8, dx, dy and the visited mask — through the non-coherent path; the owner stamps are write-only here and are
 // inspected by the verify kernel.  owner word = [epoch | rank]; epochs DEcrease from round to round and frame to frame,
 // so a newer stamp always wins over stale ones and the plane is re-initialised only when the epoch field wraps.
+#include <cstdio>
 #include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
@@ -395,7 +396,7 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     const int slot = slot0 + blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
-    const int lo = C.win_lo, hi = C.win_hi;
+    const int n_esc = C.esc_n;                                  // this round's floods that outgrew the sub-warp window (k_flood_small)
     const int warp = threadIdx.x >> 5;
     const unsigned epoch = epoch_first - (unsigned)round;
     TileTab T;
@@ -405,14 +406,190 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     // so the long floods start first and the short ones fill the gaps); the next position is requested before the
     // current flood starts so that the round trip of the atomic is hidden behind it.
     const int lane = threadIdx.x & 31;
-    int * q = &C.queue[round];
+    int * q = &C.esc_q;
+    const int * esc = S.esc + (size_t)slot * S.cap;
     int nxt = 0;
     if (lane == 0) nxt = atomicAdd(q, 1);
     while (true) {
-        const int rank = lo + __shfl_sync(0xffffffffu, nxt, 0);
-        if (rank >= hi) break;
+        const int pos = __shfl_sync(0xffffffffu, nxt, 0);
+        if (pos >= n_esc) break;
         if (lane == 0) nxt = atomicAdd(q, 1);
-        flood_one<RB>(P, S, K, C, slot, rank, epoch, T, g_off, g_left);
+        flood_one<RB>(P, S, K, C, slot, esc[pos], epoch, T, g_off, g_left);
+    }
+}
+
+// ---- sub-warp flood: 8 lanes per seed, four seeds per warp -------------------------------------------------------------
+// Most tentative regions are tiny (median 6 pixels, 95 % below 24: profiles/r2_flood_regions.md) and thin, and the seed's
+// orientation bin says which way they run.  The fast path therefore floods inside ONE 256-pixel window per seed, laid along the
+// expected line direction — WIDE: 8 rows x 32 columns for the bins of near-horizontal edges, TALL: 32 rows x 8 columns
+// otherwise — held as eight 32-bit words, one per lane of an 8-lane group: word = one line of the window along its long axis.
+// The flood step is the same register-only fixed point as in flood_tiles (complete fill along the long axis by the carry
+// trick, one shuffle step across it), 8-connectivity being symmetric under the transposition that distinguishes the layouts.
+// A region that reaches the window's outer ring may continue outside: the seed is handed to the full-tile path (k_flood_round)
+// through the round's escalation list, as are seeds whose window does not lie inside the plane.  ~12x fewer instructions and
+// 4x fewer bytes per typical flood than a 32 x 32 tile per warp.
+__device__ __forceinline__ unsigned bits4(unsigned w, int sh) { return (((w >> sh) & 0x01010101u) * 0x01020408u) >> 24; }   // 4 bytes -> 4 bits: bit i = bit `sh` of byte i
+
+template <int MINB>
+__global__ void __launch_bounds__(FL_WARPS * 32, MINB)
+k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first, int slot0, int mode)
+{
+    const int slot = slot0 + blockIdx.y;
+    FrameCtrl & C = ctrl[slot];
+    if (C.live[round] == 0 || C.flood_overflow) return;
+    const int lo = C.win_lo, hi = C.win_hi;
+    const unsigned epoch = epoch_first - (unsigned)round;
+    const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
+    const size_t so = (size_t)slot * S.cap, pbase = (size_t)slot * P.stride;
+    const float * pdx = P.dx + pbase; const float * pdy = P.dy + pbase;
+    const uint8_t * pm8 = P.mask8 + pbase; const uint8_t * pvis = P.vis + pbase;
+    unsigned * owner = P.owner + pbase;
+    unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
+    const int W = P.w, H = P.h, pitch = P.pitch;
+    int g_off = 0, g_left = 0;
+    int * q = &C.queue[round];
+    int nxt = 0;
+    if (lane == 0) nxt = atomicAdd(q, 4);
+    int guard_main = 0;
+    while (true) {
+        const int base = lo + __shfl_sync(0xffffffffu, nxt, 0);
+        if (base >= hi) break;
+        if (++guard_main > 100000) { if (lane == 0) { C.dbg_floods = base; C.dbg_big = hi; C.dbg_maxpx = lo; } break; }
+        if (lane == 0) nxt = atomicAdd(q, 4);                     // the next four, requested before this batch starts
+        const int rank = base + grp;
+        const bool valid = rank < hi;
+        const unsigned st0 = valid ? __ldcg(S.status + so + rank) : kStatusDropped;
+        const unsigned spx = valid ? S.idx[so + rank] : 0u;
+        const int sbin = valid ? S.bin[so + rank] : 0;
+        const float sthr = valid ? S.thr[so + rank] : 0.f;
+        const bool live = valid && st0 == kStatusLive;
+        const int sr = (int)(spx / (unsigned)W), sc = (int)(spx - (unsigned)sr * (unsigned)W);
+        // bins 0, 1, 2, 6, 7: the edge runs closer to the x axis (the energy weighs dy more) -> WIDE window
+        const bool wide = (sbin <= 2) || (sbin >= 6);
+        int y0 = wide ? sr - 3 : sr - 15;
+        int x0 = wide ? ((sc - 14) & ~3) : ((sc - 2) & ~3);                             // 16-byte aligned float rows
+        const bool inside = !(mode & 1) && y0 >= 0 && y0 + (wide ? 8 : 32) <= H && x0 >= 0 && x0 + (wide ? 32 : 8) <= pitch;   // mode 1 (LRB_FLOOD_SMALL_MODE=1, diagnosis): every flood takes the full-tile path
+        const bool work = live && inside;
+        if (!__any_sync(0xffffffffu, work)) {                     // nothing to flood here: committed / dropped seeds, or all four need the full path
+            const unsigned be = __ballot_sync(0xffffffffu, sub == 0 && live);
+            if (sub == 0 && live) S.esc[so + atomicAdd(&C.esc_n, 1)] = rank;
+            if (lane == 0 && be) atomicAdd(&C.floods_esc, __popc(be));
+            continue;
+        }
+        if (!work) { y0 = 0; x0 = 0; }                           // idle groups compute on a harmless window (every shift below stays in range)
+        const float sb = kSin[sbin], cb = kCos[sbin];
+        // ---- eligibility of the 256 pixels: every lane evaluates four runs of eight pixels (row-major inside the window)
+        unsigned E = 0u, V = 0u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int row = !work ? 0 : (wide ? y0 + sub : y0 + sub + 8 * k);
+            const int col = !work ? 0 : (wide ? x0 + 8 * k : x0);
+            const ptrdiff_t o = (ptrdiff_t)row * pitch + col;     // idle groups read the first pixels of the plane
+            const float4 a0 = __ldg(reinterpret_cast<const float4 *>(pdx + o)), a1 = __ldg(reinterpret_cast<const float4 *>(pdx + o) + 1);
+            const float4 b0 = __ldg(reinterpret_cast<const float4 *>(pdy + o)), b1 = __ldg(reinterpret_cast<const float4 *>(pdy + o) + 1);
+            uint2 m, v;                                           // 4-byte aligned (x0 is a multiple of 4), not 8
+            m.x = __ldg(reinterpret_cast<const unsigned *>(pm8 + o)); m.y = __ldg(reinterpret_cast<const unsigned *>(pm8 + o) + 1);
+            v.x = __ldg(reinterpret_cast<const unsigned *>(pvis + o)); v.y = __ldg(reinterpret_cast<const unsigned *>(pvis + o) + 1);
+            unsigned g = 0u;
+#define LRB_G(val_x, val_y, bit) g |= (fabsf(__fadd_rn(__fmul_rn(val_x, sb), __fmul_rn(val_y, cb))) > sthr) ? (1u << (bit)) : 0u;
+            LRB_G(a0.x, b0.x, 0) LRB_G(a0.y, b0.y, 1) LRB_G(a0.z, b0.z, 2) LRB_G(a0.w, b0.w, 3)
+            LRB_G(a1.x, b1.x, 4) LRB_G(a1.y, b1.y, 5) LRB_G(a1.z, b1.z, 6) LRB_G(a1.w, b1.w, 7)
+#undef LRB_G
+            const unsigned mb = bits4(m.x, sbin) | (bits4(m.y, sbin) << 4);
+            const unsigned vb = bits4(v.x, 0) | (bits4(v.y, 0) << 4);
+            // interior only (reference src/filter.cpp:101-107): rows 1 .. H-2, columns 1 .. W-2
+            const int c_lo = max(0, 1 - col), c_hi = min(8, W - 1 - col);
+            const unsigned cm = (row >= 1 && row < H - 1 && c_hi > c_lo) ? (((1u << c_hi) - 1u) & ~((1u << c_lo) - 1u)) : 0u;
+            E |= (g & mb & ~vb & cm) << (8 * k);
+            V |= vb << (8 * k);
+        }
+        // the seed: lane / bit in the row-major form
+        const int sy = work ? sr - y0 : 0, sx = work ? sc - x0 : 0;
+        const unsigned sbit_rm = wide ? ((sub == sy) ? (1u << sx) : 0u) : ((sub == (sy & 7)) ? (1u << (8 * (sy >> 3) + sx)) : 0u);
+        const unsigned gmask = 0xFFu << (8 * grp);
+        const unsigned seen = __ballot_sync(0xffffffffu, (V & sbit_rm) != 0u);       // evaluated by every lane (no short-circuit around a collective)
+        const bool swallowed = work && ((seen & gmask) != 0u);                       // line_detector.cpp:103
+        {   // TALL: 8 x 8 bit blocks transposed across the group -> lane = column, bit = row (computed by every lane: the four
+            // groups of a warp may use different layouts and the shuffles must stay convergent)
+            unsigned Et = E;
+#pragma unroll
+            for (int s = 4; s > 0; s >>= 1) {
+                const unsigned msk = s == 4 ? 0xF0F0F0F0u : (s == 2 ? 0xCCCCCCCCu : 0xAAAAAAAAu);
+                const unsigned t = __shfl_xor_sync(0xffffffffu, Et, s);
+                Et = (sub & s) ? ((Et & msk) | ((t >> s) & ~msk)) : ((Et & ~msk) | ((t << s) & msk));
+            }
+            E = wide ? E : Et;
+        }
+        const unsigned sbit = wide ? sbit_rm : ((sub == sx) ? (1u << sy) : 0u);
+        const bool go = work && !swallowed;
+        E = go ? (E | sbit) : 0u;                                 // the seed itself is accepted unconditionally (filter.cpp:119-122)
+        unsigned R = go ? sbit : 0u;
+        const unsigned Erev = __brev(E);
+        int guard_fl = 0;
+        while (true) {
+            if (++guard_fl > 400) { if (lane == 0) C.dbg_tiles = rank; break; }
+            const unsigned s1 = E + R;
+            const unsigned f1 = ((s1 ^ E) & E) | R;
+            const unsigned r1 = __brev(f1);
+            const unsigned s2 = Erev + r1;
+            const unsigned Hh = __brev(((s2 ^ Erev) & Erev) | r1);              // R closed along the long axis
+            const unsigned hz = Hh | (Hh << 1) | (Hh >> 1);
+            unsigned up = __shfl_up_sync(0xffffffffu, hz, 1, 8), dn = __shfl_down_sync(0xffffffffu, hz, 1, 8);
+            if (sub == 0) up = 0u;
+            if (sub == 7) dn = 0u;
+            const unsigned Rn = Hh | (E & (up | dn));
+            const bool ch = Rn != R;
+            R = Rn;
+            if (!__any_sync(0xffffffffu, ch)) break;
+        }
+        // a region on the outer ring of the window may go on outside it
+        const bool ring = (sub == 0 || sub == 7) ? (R != 0u) : ((R & 0x80000001u) != 0u);
+        const bool spilled = (__ballot_sync(0xffffffffu, ring) & gmask) != 0u;
+        const bool escalate = live && (!inside || (go && (spilled || (mode & 4))));
+        const bool done = go && !spilled && !(mode & 4);
+        int cnt = done ? __popc(R) : 0;
+        int pre = cnt;                                            // inclusive prefix inside the group
+#pragma unroll
+        for (int sft = 1; sft < 8; sft <<= 1) { const int v = __shfl_up_sync(0xffffffffu, pre, sft, 8); if (sub >= sft) pre += v; }
+        const int size = __shfl_sync(0xffffffffu, pre, 7, 8);
+        // list space for the (up to) four regions of the warp: one granule request at a time
+        const int s0 = __shfl_sync(0xffffffffu, size, 0), s1_ = __shfl_sync(0xffffffffu, size, 8), s2_ = __shfl_sync(0xffffffffu, size, 16), s3_ = __shfl_sync(0xffffffffu, size, 24);
+        const int total = s0 + s1_ + s2_ + s3_;
+        bool overflow = false;
+        if (total > g_left) {
+            const int want = max(total, kPoolGranule);
+            if (lane == 0) g_off = atomicAdd(&C.pool_cursor, want);
+            g_off = __shfl_sync(0xffffffffu, g_off, 0);
+            g_left = (g_off + want <= K.cap_pool) ? want : -1;
+        }
+        if (g_left < 0) { overflow = true; g_left = 0; }
+        const int off = g_off + (grp > 0 ? s0 : 0) + (grp > 1 ? s1_ : 0) + (grp > 2 ? s2_ : 0);
+        if (!overflow) { g_off += total; g_left -= total; }
+        if (done && !overflow && !(mode & 2)) {
+            const unsigned key = (epoch << 24) | (unsigned)rank;
+            unsigned * list = pool + off + (pre - cnt);
+            unsigned mm = R;
+            while (mm) {
+                const int b = __ffs(mm) - 1; mm &= mm - 1;
+                const int y = wide ? y0 + sub : y0 + b, x = wide ? x0 + b : x0 + sub;
+                atomicMin(owner + (size_t)y * pitch + x, key);
+                *list++ = ((unsigned)y << 16) | (unsigned)x;
+            }
+        }
+        {   // statistics: one atomic per warp and kind
+            const unsigned bd = __ballot_sync(0xffffffffu, sub == 0 && done), be = __ballot_sync(0xffffffffu, sub == 0 && escalate);
+            if (lane == 0) { if (bd) atomicAdd(&C.floods_small, __popc(bd)); if (be) atomicAdd(&C.floods_esc, __popc(be)); }
+        }
+        if (sub == 0 && live) {
+            if (swallowed) S.status[so + rank] = kStatusDropped;
+            else if (escalate) S.esc[so + atomicAdd(&C.esc_n, 1)] = rank;
+            else {
+                if (overflow) C.flood_overflow = 1;
+                S.size[so + rank] = overflow ? -1 : size;
+                S.list_head[so + rank] = off;
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -488,7 +665,7 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         const int nlo = failed ? min(firstf, hi) : hi;
         const int nhi = min(n, hi + max(0, budget - failed));
         C.win_lo = nlo; C.win_hi = nhi;
-        C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0; C.pool_cursor = 0;
+        C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0; C.pool_cursor = 0; C.esc_n = 0; C.esc_q = 0;
         C.live[round + 1] = failed + (n - hi);                       // seeds that may still have to flood
         C.rounds_run = round + 1;
     }
@@ -597,11 +774,23 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
         static const bool prune = getenv("LRB_FLOOD_NO_PRUNE") == nullptr;
         dim3 gp(max(1, min((seeds_hint + 255) / 256, 64)), ns);
         LRB_CARVEOUT(kern); LRB_CARVEOUT(k_flood_verify); LRB_CARVEOUT(k_flood_prune);
+        // the sub-warp pass takes four seeds per warp: a quarter of the warps covers the same window
+        const int sblocks = max(1, min((seeds_hint + 4 * FL_WARPS - 1) / (4 * FL_WARPS), (n_sm * 6 + ns - 1) / ns));
+        dim3 gs(sblocks, ns);
+        LRB_CARVEOUT(k_flood_small<6>);
+        static const int small_mode = [] { const char * v = getenv("LRB_FLOOD_SMALL_MODE"); return v ? atoi(v) : 0; }();
         for (int r = round_begin; r < round_end; ++r) {
             if (prune && r > 0) { k_flood_prune<<<gp, 256, 0, st>>>(P, S, ctrl, r, s0); ++launches; }
+            static const bool trace = getenv("LRB_TRACE") != nullptr;      // diagnosis: synchronise and report after every kernel of a round
+#define LRB_TRACE_SYNC(what) do { if (trace) { fprintf(stderr, "[lrb] flood round %d: %s ...", r, what); fflush(stderr); cudaError_t te = cudaStreamSynchronize(st); fprintf(stderr, " %s\n", cudaGetErrorString(te)); fflush(stderr); } } while (0)
+            k_flood_small<6><<<gs, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode);
+            LRB_TRACE_SYNC("sub-warp pass");
             kern<<<gf, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
+            LRB_TRACE_SYNC("full-tile pass");
             k_flood_verify<<<gv, 256, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
-            launches += 2;
+            LRB_TRACE_SYNC("verify");
+#undef LRB_TRACE_SYNC
+            launches += 3;
         }
     }
     return launches;                                                        // kernels launched (the engine counts them)

@@ -305,12 +305,14 @@ void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int
 }
 
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
-                   int T, cudaStream_t st)
+                   int T, cudaStream_t st, cudaEvent_t * ev_score)
 {
     for (int k = 0; k < kMaxModels; ++k) {
         launch_sampler(L, ctrl, n_slots, stream, stream_len, k, T, st);
         dim3 gs((T + SC_THREADS - 1) / SC_THREADS, n_slots);
+        if (ev_score) cudaEventRecord(ev_score[2 * k], st);
         k_score<<<gs, SC_THREADS, 0, st>>>(L, ctrl, k, T);
+        if (ev_score) cudaEventRecord(ev_score[2 * k + 1], st);
         k_refit_assign<<<n_slots, 1024, 0, st>>>(L, ctrl, k, T);
     }
     dim3 gf(8, n_slots);

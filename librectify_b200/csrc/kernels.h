@@ -28,8 +28,9 @@ void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * 
 void launch_labels(const Planes & P, const Comps & K, FrameCtrl * ctrl, int * labels, int slot, cudaStream_t st);
 // k6_ransac.cu
 void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int n_slots, float min_length, int rounds_total, bool refined, cudaStream_t st);
+// ev_score: nullptr, or 2 * kMaxModels events recorded before / after the k_score launch of each solve (per-kernel roofline)
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
-                   int T, cudaStream_t st);
+                   int T, cudaStream_t st, cudaEvent_t * ev_score = nullptr);
 // k_refine.cu
 int  launch_refine(const Comps & K, FrameCtrl * ctrl, int n_slots, cudaStream_t st);      // returns the kernels launched
 const float * refine_output(const Comps & K, int slot);                                    // merged raw segments of a slot
