@@ -48,7 +48,8 @@ typedef struct lrb_frame_info {
     int n_solves;         /* vanishing-point structures estimated (<= 4) */
     int n_obs[4];         /* observations per solve: the scoring grid is 10^4 x n_obs[k] */
     float max_magnitude;
-    int floods_small;     /* tentative floods finished inside the sub-warp window (k_flood_small), all rounds */
+    int floods_small;     /* tentative floods finished inside the 8-lane (256-pixel) window of k_flood_small, all rounds */
+    int floods_mid;       /* ... inside the 16-lane (512-pixel) window of the second pass */
     int floods_escalated; /* tentative floods handed on to the full-tile path */
 } lrb_frame_info;
 

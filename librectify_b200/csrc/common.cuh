@@ -61,7 +61,8 @@ __device__ __forceinline__ float orient_energy(float dx, float dy, int b)
 // ---- seed ordering ------------------------------------------------------------------------------------------------
 constexpr int kSeedBuckets = 4096;
 constexpr int kSampWorkers = 128, kSampRecords = 512;
-constexpr int kFloodWindowMin = 4096, kFloodWindowDiv = 6;   // seeds flooded per round: max(4096, n_seeds / 6)
+constexpr int kFloodWindowMin = 4096, kFloodWindowDiv = 6;   // steady window: max(4096, n_seeds / 6) seeds per round ...
+constexpr int kFloodWindowFirst = 256;                       // ... reached by doubling from this size in round 0
 
 // ---- per-frame control block (device memory, one per slot; zeroed by k_frame_init) -------------------------------
 constexpr int kMaxRounds = 96;
@@ -85,7 +86,8 @@ struct FrameCtrl {
     int win_live, win_first, win_blocks;   // commit-kernel scratch (live seeds left in the window, lowest of them, blocks done)
     int live[kMaxRounds + 1];  // live[r]: seeds still live after the commit of round r-1 (live[0] = n_seeds)
     int queue[kMaxRounds + 1]; // queue[r]: next window position handed out in flood round r (warps take seeds dynamically, in priority order)
-    int floods_small, floods_esc;   // statistics over all rounds: floods finished in the sub-warp window / escalated
+    int floods_small, floods_mid, floods_esc;   // statistics over all rounds: floods finished in the 8-lane / 16-lane window / handed to the full-tile path
+    int esc2_n, esc2_q;        // the same for the second (16-lane) pass -> full-tile path
     int esc_n, esc_q;          // floods of the current round that outgrew the sub-warp window (escalated to the full-tile path), next one handed out
     int fit_queue;             // next kept component handed out by the fit kernel
     int n_edges, n_merged, refine_overflow;   // `refine` post-process (k_refine.cu): collinearity edges, merged segments, edge list full
@@ -123,7 +125,7 @@ struct Planes {                 // one frame slot = one set of planes; slot s li
 
 struct Seeds {                  // per slot: s * cap
     int cap;
-    int win_min, win_div;                     // seeds flooded per round: max(win_min, n_seeds / win_div)
+    int win_min, win_div, win_first;          // seeds flooded per round: win_first in round 0, doubling up to max(win_min, n_seeds / win_div)
     unsigned * us_mag; unsigned * us_idx;     // unsorted (emission order)
     unsigned * b_mag;  unsigned * b_idx;      // bucketed
     unsigned * idx;                           // sorted by (mag desc, raster idx asc): rank -> pixel
@@ -133,7 +135,7 @@ struct Seeds {                  // per slot: s * cap
     unsigned * fail_epoch;
     int * size;
     int * list_head;                          // first pool chunk of the seed's tentative pixel list (this round)
-    int * esc;                                // ranks of this round's escalated floods (see k_flood_small)
+    int * esc; int * esc2;                    // ranks of this round's escalated floods: 8-lane pass -> 16-lane pass -> full-tile path (k_flood_small)
     int * hist; int * start; int * cursor;    // kSeedBuckets each per slot
     // raster order of the peaks and the std::sort replay (k3_replay.cu): the reference sorts its peak list, which is in raster
     // order, with std::sort (reference src/filter.cpp:174-188) — unstable, so the order of exact-magnitude ties is whatever

@@ -84,7 +84,7 @@ int make_tmap(CUtensorMap * m, CUtensorMapDataType dt, int esize, const void * b
 
 constexpr int kT = kRansacIter;
 constexpr int kLinesHead = 4096;       // segments per slot copied back together with the control block
-constexpr int kInitialRounds = 16;
+constexpr int kInitialRounds = 20;
 constexpr int kBigSlots = 64;          // concurrent long floods (global-memory tile tables) per engine
 
 } // namespace
@@ -198,7 +198,7 @@ int ensure_workspace(lrb_engine * e, int w, int h)
         e->S.idx = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.thr = carve<float>(p, (size_t)cap_seeds * G);
         e->S.bin = carve<uint8_t>(p, (size_t)cap_seeds * G); e->S.status = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.fail_epoch = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.size = carve<int>(p, (size_t)cap_seeds * G);
-        e->S.list_head = carve<int>(p, (size_t)cap_seeds * G); e->S.esc = carve<int>(p, (size_t)cap_seeds * G);
+        e->S.list_head = carve<int>(p, (size_t)cap_seeds * G); e->S.esc = carve<int>(p, (size_t)cap_seeds * G); e->S.esc2 = carve<int>(p, (size_t)cap_seeds * G);
         e->S.hist = carve<int>(p, (size_t)kSeedBuckets * G); e->S.start = carve<int>(p, (size_t)kSeedBuckets * G);
         e->S.cursor = carve<int>(p, (size_t)kSeedBuckets * G);
         e->S.rowhist = carve<int>(p, (size_t)h * G); e->S.rowstart = carve<int>(p, (size_t)h * G); e->S.rowcursor = carve<int>(p, (size_t)h * G);
@@ -234,6 +234,8 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     e->S.win_min = kFloodWindowMin; e->S.win_div = kFloodWindowDiv;
     if (const char * v = getenv("LRB_WINDOW_MIN")) e->S.win_min = std::max(1, atoi(v));
     if (const char * v = getenv("LRB_WINDOW_DIV")) e->S.win_div = std::max(1, atoi(v));
+    e->S.win_first = kFloodWindowFirst;
+    if (const char * v = getenv("LRB_WINDOW_FIRST")) e->S.win_first = std::max(1, atoi(v));
     e->S.rows = h; e->S.roww = w;
     e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->K.cap_pool = (int)std::min<size_t>(cap_pool, 0x7fffffe0); e->L.cap = cap_lines;
     e->K.big_slots = kBigSlots; e->K.big_cap = big_cap; e->K.big_bytes = big_bytes;
@@ -508,7 +510,7 @@ void fill_info(const lrb_engine * e, int i, lrb_frame_info * out)
     out->flood_rounds = C.rounds_run; out->flood_fallback = e->last_fallback[i]; out->n_solves = C.n_solves;
     for (int k = 0; k < 4; ++k) out->n_obs[k] = k < C.n_solves ? C.n_obs[k] : 0;
     unsigned g = C.gmax_bits; float f; memcpy(&f, &g, 4); out->max_magnitude = f;
-    out->floods_small = C.floods_small; out->floods_escalated = C.floods_esc;
+    out->floods_small = C.floods_small; out->floods_mid = C.floods_mid; out->floods_escalated = C.floods_esc;
 }
 
 int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, int w, int h, long long pitch,

@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(1024) k_seed_scan(Seeds S, FrameCtrl * ctrl)
         if (ctrl[slot].n_seeds > S.cap) { ctrl[slot].n_seeds = S.cap; ctrl[slot].seed_overflow = 1; }
         const int ns = ctrl[slot].n_seeds;
         ctrl[slot].live[0] = ns;
-        ctrl[slot].win_lo = 0; ctrl[slot].win_hi = min(ns, max(S.win_min, ns / S.win_div));
+        ctrl[slot].win_lo = 0; ctrl[slot].win_hi = min(ns, min(max(S.win_min, ns / S.win_div), S.win_first));
         ctrl[slot].win_live = 0; ctrl[slot].win_first = 0x7fffffff; ctrl[slot].win_blocks = 0;
     }
 }

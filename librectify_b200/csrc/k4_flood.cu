@@ -396,7 +396,7 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     const int slot = slot0 + blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
-    const int n_esc = C.esc_n;                                  // this round's floods that outgrew the sub-warp window (k_flood_small)
+    const int n_esc = C.esc2_n;                                 // this round's floods that outgrew both sub-warp windows (k_flood_small<8>, <16>)
     const int warp = threadIdx.x >> 5;
     const unsigned epoch = epoch_first - (unsigned)round;
     TileTab T;
@@ -406,8 +406,8 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     // so the long floods start first and the short ones fill the gaps); the next position is requested before the
     // current flood starts so that the round trip of the atomic is hidden behind it.
     const int lane = threadIdx.x & 31;
-    int * q = &C.esc_q;
-    const int * esc = S.esc + (size_t)slot * S.cap;
+    int * q = &C.esc2_q;
+    const int * esc = S.esc2 + (size_t)slot * S.cap;
     int nxt = 0;
     if (lane == 0) nxt = atomicAdd(q, 1);
     while (true) {
@@ -430,34 +430,44 @@ k_flood_round(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
 // 4x fewer bytes per typical flood than a 32 x 32 tile per warp.
 __device__ __forceinline__ unsigned bits4(unsigned w, int sh) { return (((w >> sh) & 0x01010101u) * 0x01020408u) >> 24; }   // 4 bytes -> 4 bits: bit i = bit `sh` of byte i
 
-template <int MINB>
+// G = lanes per seed (8: first pass over the round's window, 256-pixel windows; 16: second pass over what the first pass
+// escalated, 512-pixel windows 16 x 32 / 32 x 16).  Ranks come from the window (src == nullptr) or from an escalation list;
+// floods that outgrow this pass's window go to the list `dst` (consumed by the next pass / the full-tile kernel).
+template <int G, int MINB>
 __global__ void __launch_bounds__(FL_WARPS * 32, MINB)
-k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first, int slot0, int mode)
+k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first, int slot0, int mode, int last_pass)
 {
+    constexpr int NG = 32 / G;                                    // seeds per warp
+    constexpr int RUNS_PER_ROW = G / 8;                           // TALL: runs of eight pixels per window row
     const int slot = slot0 + blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.live[round] == 0 || C.flood_overflow) return;
-    const int lo = C.win_lo, hi = C.win_hi;
     const unsigned epoch = epoch_first - (unsigned)round;
-    const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
+    const int lane = threadIdx.x & 31, sub = lane % G, grp = lane / G;
     const size_t so = (size_t)slot * S.cap, pbase = (size_t)slot * P.stride;
+    // first pass: the window's ranks; second pass: the first pass's escalation list
+    const bool first_pass = (G == 8);
+    const int lo = first_pass ? C.win_lo : 0, hi = first_pass ? C.win_hi : C.esc_n;
+    const int * src = S.esc + so;
+    // what this pass cannot finish goes to the next pass's list, from the last sub-warp pass to the full-tile kernel's
+    int * dst = last_pass ? S.esc2 + so : S.esc + so;
+    int * dst_n = last_pass ? &C.esc2_n : &C.esc_n;
+    int * q = first_pass ? &C.queue[round] : &C.esc_q;
     const float * pdx = P.dx + pbase; const float * pdy = P.dy + pbase;
     const uint8_t * pm8 = P.mask8 + pbase; const uint8_t * pvis = P.vis + pbase;
     unsigned * owner = P.owner + pbase;
     unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
     const int W = P.w, H = P.h, pitch = P.pitch;
     int g_off = 0, g_left = 0;
-    int * q = &C.queue[round];
     int nxt = 0;
-    if (lane == 0) nxt = atomicAdd(q, 4);
-    int guard_main = 0;
+    if (lane == 0) nxt = atomicAdd(q, NG);
     while (true) {
         const int base = lo + __shfl_sync(0xffffffffu, nxt, 0);
         if (base >= hi) break;
-        if (++guard_main > 100000) { if (lane == 0) { C.dbg_floods = base; C.dbg_big = hi; C.dbg_maxpx = lo; } break; }
-        if (lane == 0) nxt = atomicAdd(q, 4);                     // the next four, requested before this batch starts
-        const int rank = base + grp;
-        const bool valid = rank < hi;
+        if (lane == 0) nxt = atomicAdd(q, NG);                    // the next batch, requested before this one starts
+        const int pos = base + grp;
+        const bool valid = pos < hi;
+        const int rank = !valid ? 0 : (first_pass ? pos : src[pos]);
         const unsigned st0 = valid ? __ldcg(S.status + so + rank) : kStatusDropped;
         const unsigned spx = valid ? S.idx[so + rank] : 0u;
         const int sbin = valid ? S.bin[so + rank] : 0;
@@ -466,24 +476,24 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
         const int sr = (int)(spx / (unsigned)W), sc = (int)(spx - (unsigned)sr * (unsigned)W);
         // bins 0, 1, 2, 6, 7: the edge runs closer to the x axis (the energy weighs dy more) -> WIDE window
         const bool wide = (sbin <= 2) || (sbin >= 6);
-        int y0 = wide ? sr - 3 : sr - 15;
-        int x0 = wide ? ((sc - 14) & ~3) : ((sc - 2) & ~3);                             // 16-byte aligned float rows
-        const bool inside = !(mode & 1) && y0 >= 0 && y0 + (wide ? 8 : 32) <= H && x0 >= 0 && x0 + (wide ? 32 : 8) <= pitch;   // mode 1 (LRB_FLOOD_SMALL_MODE=1, diagnosis): every flood takes the full-tile path
+        int y0 = wide ? sr - (G / 2 - 1) : sr - 15;
+        int x0 = wide ? ((sc - 14) & ~3) : ((sc - (G / 2 - 2)) & ~3);                   // 16-byte aligned float rows
+        const bool inside = !(mode & 1) && y0 >= 0 && y0 + (wide ? G : 32) <= H && x0 >= 0 && x0 + (wide ? 32 : G) <= pitch;   // mode 1 (LRB_FLOOD_SMALL_MODE=1, diagnosis): every flood takes the full-tile path
         const bool work = live && inside;
-        if (!__any_sync(0xffffffffu, work)) {                     // nothing to flood here: committed / dropped seeds, or all four need the full path
+        if (!__any_sync(0xffffffffu, work)) {                     // nothing to flood here: committed / dropped seeds, or all need the next pass
             const unsigned be = __ballot_sync(0xffffffffu, sub == 0 && live);
-            if (sub == 0 && live) S.esc[so + atomicAdd(&C.esc_n, 1)] = rank;
-            if (lane == 0 && be) atomicAdd(&C.floods_esc, __popc(be));
+            if (sub == 0 && live) dst[atomicAdd(dst_n, 1)] = rank;
+            if (lane == 0 && be && last_pass) atomicAdd(&C.floods_esc, __popc(be));
             continue;
         }
         if (!work) { y0 = 0; x0 = 0; }                           // idle groups compute on a harmless window (every shift below stays in range)
         const float sb = kSin[sbin], cb = kCos[sbin];
-        // ---- eligibility of the 256 pixels: every lane evaluates four runs of eight pixels (row-major inside the window)
+        // ---- eligibility of the window: every lane evaluates four runs of eight pixels (row-major inside the window)
         unsigned E = 0u, V = 0u;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const int row = !work ? 0 : (wide ? y0 + sub : y0 + sub + 8 * k);
-            const int col = !work ? 0 : (wide ? x0 + 8 * k : x0);
+            const int row = !work ? 0 : (wide ? y0 + sub : y0 + sub + G * (k / RUNS_PER_ROW));
+            const int col = !work ? 0 : (wide ? x0 + 8 * k : x0 + 8 * (k % RUNS_PER_ROW));
             const ptrdiff_t o = (ptrdiff_t)row * pitch + col;     // idle groups read the first pixels of the plane
             const float4 a0 = __ldg(reinterpret_cast<const float4 *>(pdx + o)), a1 = __ldg(reinterpret_cast<const float4 *>(pdx + o) + 1);
             const float4 b0 = __ldg(reinterpret_cast<const float4 *>(pdy + o)), b1 = __ldg(reinterpret_cast<const float4 *>(pdy + o) + 1);
@@ -505,16 +515,16 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
         }
         // the seed: lane / bit in the row-major form
         const int sy = work ? sr - y0 : 0, sx = work ? sc - x0 : 0;
-        const unsigned sbit_rm = wide ? ((sub == sy) ? (1u << sx) : 0u) : ((sub == (sy & 7)) ? (1u << (8 * (sy >> 3) + sx)) : 0u);
-        const unsigned gmask = 0xFFu << (8 * grp);
+        const unsigned sbit_rm = wide ? ((sub == sy) ? (1u << sx) : 0u) : ((sub == (sy % G)) ? (1u << (G * (sy / G) + sx)) : 0u);
+        const unsigned gmask = (G == 8 ? 0xFFu : 0xFFFFu) << (G * grp);
         const unsigned seen = __ballot_sync(0xffffffffu, (V & sbit_rm) != 0u);       // evaluated by every lane (no short-circuit around a collective)
         const bool swallowed = work && ((seen & gmask) != 0u);                       // line_detector.cpp:103
-        {   // TALL: 8 x 8 bit blocks transposed across the group -> lane = column, bit = row (computed by every lane: the four
+        {   // TALL: G x G bit blocks transposed across the group -> lane = column, bit = row (computed by every lane: the
             // groups of a warp may use different layouts and the shuffles must stay convergent)
             unsigned Et = E;
 #pragma unroll
-            for (int s = 4; s > 0; s >>= 1) {
-                const unsigned msk = s == 4 ? 0xF0F0F0F0u : (s == 2 ? 0xCCCCCCCCu : 0xAAAAAAAAu);
+            for (int s = G / 2; s > 0; s >>= 1) {
+                const unsigned msk = s == 8 ? 0xFF00FF00u : (s == 4 ? 0xF0F0F0F0u : (s == 2 ? 0xCCCCCCCCu : 0xAAAAAAAAu));
                 const unsigned t = __shfl_xor_sync(0xffffffffu, Et, s);
                 Et = (sub & s) ? ((Et & msk) | ((t >> s) & ~msk)) : ((Et & ~msk) | ((t << s) & msk));
             }
@@ -527,34 +537,35 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
         const unsigned Erev = __brev(E);
         int guard_fl = 0;
         while (true) {
-            if (++guard_fl > 400) { if (lane == 0) C.dbg_tiles = rank; break; }
+            if (++guard_fl > 64 * G) { if (lane == 0) C.dbg_tiles = rank; break; }     // cannot happen: R grows monotonically inside E
             const unsigned s1 = E + R;
             const unsigned f1 = ((s1 ^ E) & E) | R;
             const unsigned r1 = __brev(f1);
             const unsigned s2 = Erev + r1;
             const unsigned Hh = __brev(((s2 ^ Erev) & Erev) | r1);              // R closed along the long axis
             const unsigned hz = Hh | (Hh << 1) | (Hh >> 1);
-            unsigned up = __shfl_up_sync(0xffffffffu, hz, 1, 8), dn = __shfl_down_sync(0xffffffffu, hz, 1, 8);
+            unsigned up = __shfl_up_sync(0xffffffffu, hz, 1, G), dn = __shfl_down_sync(0xffffffffu, hz, 1, G);
             if (sub == 0) up = 0u;
-            if (sub == 7) dn = 0u;
+            if (sub == G - 1) dn = 0u;
             const unsigned Rn = Hh | (E & (up | dn));
             const bool ch = Rn != R;
             R = Rn;
             if (!__any_sync(0xffffffffu, ch)) break;
         }
         // a region on the outer ring of the window may go on outside it
-        const bool ring = (sub == 0 || sub == 7) ? (R != 0u) : ((R & 0x80000001u) != 0u);
+        const bool ring = (sub == 0 || sub == G - 1) ? (R != 0u) : ((R & 0x80000001u) != 0u);
         const bool spilled = (__ballot_sync(0xffffffffu, ring) & gmask) != 0u;
         const bool escalate = live && (!inside || (go && (spilled || (mode & 4))));
         const bool done = go && !spilled && !(mode & 4);
         int cnt = done ? __popc(R) : 0;
         int pre = cnt;                                            // inclusive prefix inside the group
 #pragma unroll
-        for (int sft = 1; sft < 8; sft <<= 1) { const int v = __shfl_up_sync(0xffffffffu, pre, sft, 8); if (sub >= sft) pre += v; }
-        const int size = __shfl_sync(0xffffffffu, pre, 7, 8);
-        // list space for the (up to) four regions of the warp: one granule request at a time
-        const int s0 = __shfl_sync(0xffffffffu, size, 0), s1_ = __shfl_sync(0xffffffffu, size, 8), s2_ = __shfl_sync(0xffffffffu, size, 16), s3_ = __shfl_sync(0xffffffffu, size, 24);
-        const int total = s0 + s1_ + s2_ + s3_;
+        for (int sft = 1; sft < G; sft <<= 1) { const int v = __shfl_up_sync(0xffffffffu, pre, sft, G); if (sub >= sft) pre += v; }
+        const int size = __shfl_sync(0xffffffffu, pre, G - 1, G);
+        // list space for the regions of the warp: one granule request at a time
+        int total = 0, before = 0;
+#pragma unroll
+        for (int gi = 0; gi < NG; ++gi) { const int sg = __shfl_sync(0xffffffffu, size, gi * G); total += sg; before += (gi < grp) ? sg : 0; }
         bool overflow = false;
         if (total > g_left) {
             const int want = max(total, kPoolGranule);
@@ -563,7 +574,7 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
             g_left = (g_off + want <= K.cap_pool) ? want : -1;
         }
         if (g_left < 0) { overflow = true; g_left = 0; }
-        const int off = g_off + (grp > 0 ? s0 : 0) + (grp > 1 ? s1_ : 0) + (grp > 2 ? s2_ : 0);
+        const int off = g_off + before;
         if (!overflow) { g_off += total; g_left -= total; }
         if (done && !overflow && !(mode & 2)) {
             const unsigned key = (epoch << 24) | (unsigned)rank;
@@ -578,11 +589,11 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
         }
         {   // statistics: one atomic per warp and kind
             const unsigned bd = __ballot_sync(0xffffffffu, sub == 0 && done), be = __ballot_sync(0xffffffffu, sub == 0 && escalate);
-            if (lane == 0) { if (bd) atomicAdd(&C.floods_small, __popc(bd)); if (be) atomicAdd(&C.floods_esc, __popc(be)); }
+            if (lane == 0) { if (bd) atomicAdd(first_pass ? &C.floods_small : &C.floods_mid, __popc(bd)); if (be && last_pass) atomicAdd(&C.floods_esc, __popc(be)); }
         }
         if (sub == 0 && live) {
             if (swallowed) S.status[so + rank] = kStatusDropped;
-            else if (escalate) S.esc[so + atomicAdd(&C.esc_n, 1)] = rank;
+            else if (escalate) dst[atomicAdd(dst_n, 1)] = rank;
             else {
                 if (overflow) C.flood_overflow = 1;
                 S.size[so + rank] = overflow ? -1 : size;
@@ -661,11 +672,13 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         __threadfence();
         const int failed = atomicAdd(&C.win_live, 0);                 // window seeds that stay live (out-prioritised this round)
         const int firstf = atomicMin(&C.win_first, 0x7fffffff);
-        const int budget = max(S.win_min, n / S.win_div);
+        // seeds flooded per round: small at first — the strongest seeds own the long lines, and every other seed on such a line
+        // would flood the whole line again, only to lose against the line's strongest seed — then doubling up to the steady size
+        const int budget = min(max(S.win_min, n / S.win_div), S.win_first << min(round + 1, 16));
         const int nlo = failed ? min(firstf, hi) : hi;
         const int nhi = min(n, hi + max(0, budget - failed));
         C.win_lo = nlo; C.win_hi = nhi;
-        C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0; C.pool_cursor = 0; C.esc_n = 0; C.esc_q = 0;
+        C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0; C.pool_cursor = 0; C.esc_n = 0; C.esc_q = 0; C.esc2_n = 0; C.esc2_q = 0;
         C.live[round + 1] = failed + (n - hi);                       // seeds that may still have to flood
         C.rounds_run = round + 1;
     }
@@ -774,17 +787,27 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
         static const bool prune = getenv("LRB_FLOOD_NO_PRUNE") == nullptr;
         dim3 gp(max(1, min((seeds_hint + 255) / 256, 64)), ns);
         LRB_CARVEOUT(kern); LRB_CARVEOUT(k_flood_verify); LRB_CARVEOUT(k_flood_prune);
-        // the sub-warp pass takes four seeds per warp: a quarter of the warps covers the same window
+        // the sub-warp passes take four / two seeds per warp
         const int sblocks = max(1, min((seeds_hint + 4 * FL_WARPS - 1) / (4 * FL_WARPS), (n_sm * 6 + ns - 1) / ns));
-        dim3 gs(sblocks, ns);
-        LRB_CARVEOUT(k_flood_small<6>);
+        const int mblocks = max(1, min((seeds_hint + 2 * FL_WARPS - 1) / (2 * FL_WARPS), (n_sm * 6 + ns - 1) / ns / 2));
+        dim3 gs(sblocks, ns), gm(mblocks, ns);
+        LRB_CARVEOUT((k_flood_small<8, 6>)); LRB_CARVEOUT((k_flood_small<16, 6>));
         static const int small_mode = [] { const char * v = getenv("LRB_FLOOD_SMALL_MODE"); return v ? atoi(v) : 0; }();
         for (int r = round_begin; r < round_end; ++r) {
             if (prune && r > 0) { k_flood_prune<<<gp, 256, 0, st>>>(P, S, ctrl, r, s0); ++launches; }
             static const bool trace = getenv("LRB_TRACE") != nullptr;      // diagnosis: synchronise and report after every kernel of a round
 #define LRB_TRACE_SYNC(what) do { if (trace) { fprintf(stderr, "[lrb] flood round %d: %s ...", r, what); fflush(stderr); cudaError_t te = cudaStreamSynchronize(st); fprintf(stderr, " %s\n", cudaGetErrorString(te)); fflush(stderr); } } while (0)
-            k_flood_small<6><<<gs, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode);
-            LRB_TRACE_SYNC("sub-warp pass");
+            // LRB_FLOOD_MID=1 adds the 16-lane pass (512-pixel windows) between the two: measured on B200 it finishes only ~30 % of
+            // what the 8-lane pass escalates (those floods are long lines, not slightly larger blobs) and costs 7 % of the job
+            // throughput (profiles/r2_flood_regions.md), so it is off by default
+            static const bool mid = [] { const char * v = getenv("LRB_FLOOD_MID"); return v && atoi(v) != 0; }();
+            k_flood_small<8, 6><<<gs, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode, mid ? 0 : 1);
+            LRB_TRACE_SYNC("sub-warp pass (8 lanes)");
+            if (mid) {
+                k_flood_small<16, 6><<<gm, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode, 1);
+                LRB_TRACE_SYNC("sub-warp pass (16 lanes)");
+                ++launches;
+            }
             kern<<<gf, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
             LRB_TRACE_SYNC("full-tile pass");
             k_flood_verify<<<gv, 256, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0);
