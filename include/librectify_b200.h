@@ -185,6 +185,14 @@ LRB_API void lrb_fit_vanishing_point(const lrb_segment * lines, int n_lines, int
 LRB_API void lrb_assign_to_group(const lrb_segment * lines, int n_lines, lrb_segment * new_lines, int n_new_lines,
                                  float angular_tolerance_deg);
 
+/* The two auxiliary functions on the device, for line sets large enough to be worth the trip (host arrays in,
+ * host results out; same arithmetic as the host versions above, bit-identical results):
+ *   lrb_fit_vanishing_point_device   reference src/interface.cpp:211-215 (group > 0: that group's lines, otherwise all lines)
+ *   lrb_assign_to_group_device       reference src/interface.cpp:218-265 */
+LRB_API int lrb_fit_vanishing_point_device(lrb_engine * e, const lrb_segment * lines, int n_lines, int group, lrb_point * out);
+LRB_API int lrb_assign_to_group_device(lrb_engine * e, const lrb_segment * lines, int n_lines, lrb_segment * new_lines, int n_new_lines,
+                                       float angular_tolerance_deg);
+
 /* ---- the reference's dormant Hough-voted estimator ---------------------------------------------
  * LinePencilModel::get_weights (reference src/line_pencil.cpp:47-86: 20 000 pair intersections voted into a 65 x 65
  * accumulator, weight = inclination^4 towards the winning cell's direction) and DirectEstimator::solve (reference

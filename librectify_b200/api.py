@@ -90,6 +90,8 @@ def load_library(path: str | None = None):
     lib.lrb_warp_perspective_u8.argtypes = [vp, vp, ip, ip, ip, ip, ll, vp, ip, vp, ip, ip, ip, ll]
     lib.lrb_autorectify_u8.argtypes = [vp, vp, ip, ip, ip, ll, fp, ip, vp, fp, vp, vp, ip, C.POINTER(ip), vp, C.c_size_t, C.POINTER(ip), C.POINTER(ip)]
     lib.lrb_direct_estimate.argtypes = [vp, vp, ip, vp, ip, vp, vp, vp]
+    lib.lrb_fit_vanishing_point_device.argtypes = [vp, vp, ip, ip, vp]
+    lib.lrb_assign_to_group_device.argtypes = [vp, vp, ip, vp, ip, fp]
     lib.lrb_stage_fetch.argtypes = [vp, ip, ip, vp, C.c_size_t]; lib.lrb_stage_fetch.restype = ll
     lib.lrb_profile_enable.argtypes = [vp, ip]; lib.lrb_profile_enable.restype = None
     lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None
@@ -370,6 +372,20 @@ class Engine:
             shape = (wh.value, ww.value) if a.ndim == 2 else (wh.value, ww.value, ch)
             warped = buf[: wh.value * ww.value * ch].reshape(shape).copy()
         return warped, tf[0], lines[: min(n.value, cap)].copy()
+
+    def fit_vanishing_point(self, lines: np.ndarray, group: int):
+        """fit_vanishing_point (reference src/interface.cpp:211-215) computed on the device"""
+        ln = np.ascontiguousarray(lines, SEG_DTYPE)
+        out = np.zeros(3, np.float32)
+        self._check(self.lib.lrb_fit_vanishing_point_device(self.h, ln.ctypes.data, len(ln), int(group), out.ctypes.data))
+        return tuple(float(v) for v in out)
+
+    def assign_to_group(self, lines: np.ndarray, new_lines: np.ndarray, angular_tolerance: float) -> np.ndarray:
+        """assign_to_group (reference src/interface.cpp:218-265) computed on the device"""
+        ln = np.ascontiguousarray(lines, SEG_DTYPE)
+        new = np.ascontiguousarray(new_lines, SEG_DTYPE).copy()
+        self._check(self.lib.lrb_assign_to_group_device(self.h, ln.ctypes.data, len(ln), new.ctypes.data, len(new), C.c_float(angular_tolerance)))
+        return new
 
     def direct_estimate(self, lines: np.ndarray, idx: np.ndarray | None = None):
         """The reference's Hough-voted DirectEstimator (src/line_pencil.cpp:47-86, src/estimator.h:82-96).

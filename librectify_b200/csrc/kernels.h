@@ -57,6 +57,11 @@ int hough_hypotheses();
 void launch_hough_direct(const float * seg7, int n_lines, const int * idx, int m, const unsigned * raw, int n_raw,
                          float * h, float * anchor, float * dir, float * len, int * draws, int * hyp_cell, float * hyp_val,
                          float * weights, int * inl, void * out, cudaStream_t st);
+// k_aux.cu: fit_vanishing_point / assign_to_group on the device
+void launch_aux_model(const float * seg7, int n, unsigned * box4, float * h, float * len, float * norm3, cudaStream_t st);
+void launch_aux_common_points(const float * seg7, int n, const float * h, const float * len, const float * norm3,
+                              const int * groups, int n_groups, bool all, float * out, cudaStream_t st);
+void launch_aux_assign(float * fresh7, int n_fresh, const int * groups, const float * vps, int n_groups, float thr, cudaStream_t st);
 // k_warp.cu
 struct WarpMatrix { double m[9]; };    // destination -> source map, row-major (what cv::warpPerspective uses after inverting H)
 void launch_warp_perspective_u8(const unsigned char * src, int sw, int sh, long long spitch, int channels, unsigned char * dst, int dw, int dh,
