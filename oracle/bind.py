@@ -223,6 +223,17 @@ class _StageLib:
         self._f("direct_solve")(C.c_void_p(segs.ctypes.data), C.c_int(len(segs)), _ip(idx), C.c_int(len(idx)), _fp(out))
         return out
 
+    def prosac_solve(self, segs, idx, tol, seed=0, trace=False):
+        """PROSAC_Estimator<LinePencilModel>::solve (reference src/prosac.h:104-299) on lines ``idx`` of ``segs``"""
+        segs = np.ascontiguousarray(segs); idx = np.ascontiguousarray(idx, np.int32)
+        self.set_seed(seed)
+        out = np.zeros(3, np.float32); tr = np.zeros(31, np.int32)
+        self._f("prosac_solve")(C.c_void_p(segs.ctypes.data), C.c_int(len(segs)), _ip(idx), C.c_int(len(idx)), C.c_float(tol), _fp(out), _ip(tr))
+        if trace:
+            return out, dict(iterations=int(tr[0]), n_final=int(tr[1]), n_star=int(tr[2]), I_N_best=int(tr[3]),
+                             samples=tr[4:22].reshape(9, 2).copy(), I_N=tr[22:31].copy())
+        return out
+
     def choice_knuth(self, seed, n, count):
         pairs = np.zeros((count, 2), np.int32); nxt = C.c_uint(0)
         draws = self._f("choice_knuth")(C.c_uint(seed), C.c_int(n), C.c_int(count), _ip(pairs), C.byref(nxt))

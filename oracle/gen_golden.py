@@ -121,9 +121,37 @@ def hough_case(ref: Ref) -> dict:
     return out
 
 
+PROSAC_TOL = float(np.float32(1.0) - np.float32(np.cos(np.float32(2.0) / np.float32(180) * np.float32(np.pi))))   # 1 - cos(2 deg), line_pencil.cpp:143-146
+
+
+def prosac_case(ref: Ref) -> dict:
+    """dormant estimator (SURVEY.md §8 f3): PROSAC_Estimator<LinePencilModel>::solve of the compiled reference (reference
+    src/prosac.h:104-299, instantiated by oracle/ref_harness.cpp, generator seeded through the random_device shim) on the
+    segments of the committed fixtures, several index lists and seeds"""
+    out = {}
+    names = []
+    for name in ("doc_image", "synth_320x240", "synth_640x360", "ingest_u8"):
+        g = np.load(os.path.join(GOLD, name + ".npz"))
+        segs = g["segs"] if "segs" in g.files else g["lines"]
+        n = len(segs)
+        lists = {"all": np.arange(n, dtype=np.int32), "third": np.arange(0, n, 3, dtype=np.int32),
+                 "rest": np.nonzero(segs["group_id"] != 0)[0].astype(np.int32), "dozen": np.arange(40, 52, dtype=np.int32)}
+        for k, idx in lists.items():
+            for seed in (0, 77):
+                tag = f"{name}:{k}:{seed}"; names.append(tag)
+                out[tag + ":idx"] = idx
+                out[tag + ":vp"] = ref.prosac_solve(segs, idx, PROSAC_TOL, seed)
+    out["cases"] = np.array(names)
+    out["tol"] = np.float32(PROSAC_TOL)
+    return out
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = Ref("canon")
+    if "--prosac-only" in sys.argv:                       # added after the other fixtures were committed: leave those untouched
+        np.savez_compressed(os.path.join(GOLD, "prosac.npz"), **prosac_case(ref))
+        return
     if "--hough-only" in sys.argv:                        # added after the other fixtures were committed: leave those untouched
         np.savez_compressed(os.path.join(GOLD, "hough.npz"), **hough_case(ref))
         return
@@ -182,6 +210,7 @@ def main():
     np.savez_compressed(os.path.join(GOLD, "refine.npz"), **refine_case(ref))
     np.savez_compressed(os.path.join(GOLD, "ingest_u8.npz"), **ingest_case(ref))
     np.savez_compressed(os.path.join(GOLD, "hough.npz"), **hough_case(ref))
+    np.savez_compressed(os.path.join(GOLD, "prosac.npz"), **prosac_case(ref))
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

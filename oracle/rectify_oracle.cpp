@@ -8,6 +8,7 @@
 #include "rectify_oracle.h"
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstring>
 #include <deque>
@@ -630,6 +631,110 @@ void direct_solve(const Model & M, const vector<int> & idx, float out[3])
     fit_optimal(M, inl, out);
 }
 
+/* ---- f3 (dormant in the reference): PROSAC_Estimator<LinePencilModel>::solve, reference src/prosac.h:104-299 -------------
+ * Progressive sampling (Chum & Matas) over the listed lines sorted by their Hough weight (argsort: std::stable_sort,
+ * descending, src/utils.h:36-44).  With the class defaults (p_good_sample 0.9, max_outlier_proportion 0.5, m = 2) the
+ * iteration bound is T_N = niter_RANSAC(0.9, 0.5, 2) = 9, so at most nine hypotheses are ever scored.
+ * Quirks kept: the semi-random sample takes `u_n` as idx(n) — one past the paper's u_n (src/prosac.h:175) — which reads
+ * beyond the list when n == N (possible only for N <= 11); this restatement requires N >= 12 like the device code. */
+int niter_ransac(double p, double epsilon, int s, int Nmax)                  /* prosac.h:30-54 */
+{
+    if (Nmax == -1) Nmax = INT_MAX;
+    if (epsilon <= 0.) return 1;
+    double logarg = -std::exp(s * std::log(1. - epsilon));
+    double logval = std::log(1. + logarg);
+    double N = std::log(1. - p) / logval;
+    if (logval < 0. && N < Nmax) return (int)std::ceil(N);
+    return Nmax;
+}
+
+void choice_knuth_general(int N, int n, MT19937 & rng, int * out)            /* math_utils.cpp:14-39, any subset size */
+{
+    int t = 0, m = 0;
+    while (m < n) {
+        uint64_t k = canonical_k(rng.next());
+        if (uint64_t(N - t) * k >= (uint64_t(n - m) << 32)) { t++; }
+        else { out[m] = t; t++; m++; }
+    }
+}
+
+struct ProsacTrace { int iterations; int n_final; int n_star; int I_N_best; int samples[9][2]; int I_N[9]; };
+
+void prosac_solve(const Model & M, const vector<int> & indices, float tol, unsigned seed, float out[3], ProsacTrace * tr)
+{
+    const float eta = 0.05f, beta = 0.01f, psi = 0.02f, p_good_sample = 0.9f, max_outlier_proportion = 0.5f;   /* prosac.h:62-66 */
+    static const float chi2_table[20] = { INFINITY, 6.6348966f, 5.41189443f, 4.70929225f, 4.21788459f, 3.84145882f, 3.5373846f, 3.28302029f,
+        3.06490172f, 2.8743734f, 2.70554345f, 2.55422131f, 2.41732093f, 2.29250453f, 2.17795916f, 2.07225086f, 1.97422609f, 1.88294329f,
+        1.79762406f, 1.71761761f };
+    const float chi2_value = chi2_table[(int)std::floor(std::min(std::max(2 * psi, 0.01f), 0.2f) * 100)];          /* prosac.h:91-95,103 */
+    auto Imin = [&](int m, int n) {                                             /* prosac.h:78-83 */
+        double mu = n * beta;
+        double sigma = std::sqrt((double)(n * beta * (1 - beta)));
+        return (int)std::ceil(m + mu + sigma * std::sqrt((double)chi2_value));
+    };
+    vector<float> w; int cell[2];
+    get_weights(M, indices, w, cell);
+    const int N = int(indices.size());
+    vector<int> order(N);
+    for (int i = 0; i < N; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return w[a] > w[b]; });
+    vector<int> idx(N);
+    for (int i = 0; i < N; ++i) idx[i] = indices[order[i]];
+    const int m = 2;
+    const int T_N = niter_ransac(p_good_sample, max_outlier_proportion, m, -1);
+    int n_star = N, I_n_star = 0, I_N_best = 0, t = 0, n = m, T_n_prime = 1, k_n_star = T_N;
+    const int I_N_min = (1. - max_outlier_proportion) * N;
+    double T_n = T_N;
+    for (int i = 0; i < m; i++) T_n *= (double)(n - i) / (N - i);
+    MT19937 rng(seed);
+    float p_best[3] = {0, 0, 0};
+    vector<unsigned char> best_in; bool have_best = false;
+    vector<unsigned char> isIn(N);
+    if (tr) { std::memset(tr, 0, sizeof *tr); }
+    while (((I_N_best < I_N_min) || t <= k_n_star) && t < T_N) {
+        t = t + 1;
+        if ((t > T_n_prime) && (n < n_star)) {
+            double T_nplus1 = (T_n * (n + 1)) / (n + 1 - m);
+            n = n + 1;
+            T_n_prime = T_n_prime + std::ceil(T_nplus1 - T_n);
+            T_n = T_nplus1;
+        }
+        int sample[2];
+        if (t > T_n_prime) choice_knuth_general(n, m, rng, sample);
+        else { choice_knuth_general(n - 1, m - 1, rng, sample); sample[m - 1] = n; }
+        if (tr) { tr->samples[t - 1][0] = sample[0]; tr->samples[t - 1][1] = sample[1]; tr->I_N[t - 1] = -1; tr->iterations = t; }
+        const int a = idx[sample[0]], b = idx[sample[1]];
+        if (!sample_check(M, a, b)) continue;
+        float p_t[3]; fit_pair(M, a, b, p_t);
+        int I_N = 0;
+        for (int i = 0; i < N; ++i) { isIn[i] = line_error(M, idx[i], p_t) < tol; I_N += isIn[i]; }
+        if (tr) tr->I_N[t - 1] = I_N;
+        if (I_N > I_N_best) {
+            I_N_best = I_N;
+            p_best[0] = p_t[0]; p_best[1] = p_t[1]; p_best[2] = p_t[2];
+            best_in = isIn; have_best = true;
+            int n_best = N, I_n_best = I_N;
+            double epsilon_n_best = (double)I_n_best / n_best;
+            for (int n_test = N, I_n_test = I_N; n_test > m; n_test--) {
+                if ((I_n_test * n_best > I_n_best * n_test) &&
+                    (I_n_test > epsilon_n_best * n_test + std::sqrt(n_test * epsilon_n_best * (1. - epsilon_n_best) * 2.706))) {
+                    if (I_n_test < Imin(m, n_test)) break;
+                    n_best = n_test; I_n_best = I_n_test; epsilon_n_best = (double)I_n_best / n_best;
+                }
+                I_n_test -= isIn[n_test - 1];
+            }
+            if (I_n_best * n_star > I_n_star * n_best) {
+                n_star = n_best; I_n_star = I_n_best;
+                k_n_star = niter_ransac(1. - eta, 1. - I_n_star / (double)n_star, m, T_N);
+            }
+        }
+    }
+    if (tr) { tr->n_final = n; tr->n_star = n_star; tr->I_N_best = I_N_best; }
+    vector<int> inl;
+    if (have_best) for (int i = 0; i < N; ++i) if (best_in[i]) inl.push_back(idx[i]);
+    fit_optimal(M, inl, out);                                                   /* empty list (no scored sample) -> all lines */
+}
+
 float cos_threshold(float deg) { return 1.0f - std::cos(deg / 180.f * float(M_PI)); }      /* line_pencil.cpp:143-146 */
 
 struct Trace { int T; int * samples; float * scores; int * n_obs; int * winner; float * best_h; float * refined; };
@@ -930,6 +1035,13 @@ void orc_direct_solve(const OrcLineSegment * lines, int n, const int * idx, int 
 {
     Model M; build_model(lines, n, M);
     direct_solve(M, vector<int>(idx, idx + n_idx), out3);
+}
+
+/* PROSAC_Estimator::solve (prosac.h:104-299) on the listed lines; trace (may be null): 4 + 18 + 9 ints, see ProsacTrace */
+void orc_prosac_solve(const OrcLineSegment * lines, int n, const int * idx, int n_idx, float tol, float * out3, int * trace)
+{
+    Model M; build_model(lines, n, M);
+    prosac_solve(M, vector<int>(idx, idx + n_idx), tol, g_seed, out3, reinterpret_cast<ProsacTrace *>(trace));
 }
 
 long long orc_choice_knuth(unsigned seed, int n, int count, int * pairs, unsigned * next_raw)

@@ -45,6 +45,8 @@ void orc_fit_optimal(const OrcLineSegment * lines, int n, const int * idx, int n
 /* dormant estimator: LinePencilModel::get_weights (line_pencil.cpp:47-86), DirectEstimator::solve (estimator.h:82-96) */
 void orc_get_weights(const OrcLineSegment * lines, int n, const int * idx, int n_idx, float * w_out);
 void orc_direct_solve(const OrcLineSegment * lines, int n, const int * idx, int n_idx, float * out3);
+/* dormant estimator: PROSAC_Estimator<LinePencilModel>::solve (prosac.h:104-299); trace: 31 ints or null */
+void orc_prosac_solve(const OrcLineSegment * lines, int n, const int * idx, int n_idx, float tol, float * out3, int * trace);
 long long orc_choice_knuth(unsigned seed, int n, int count, int * pairs, unsigned * next_raw);
 void orc_estimate_line_pencils(OrcLineSegment * lines, int n, int num_threads);
 void orc_fit_line_parameters(const float * X, const float * w, int n, OrcLineSegment * out);

@@ -32,6 +32,10 @@
 #include "transform.h"
 #include "math_utils.h"
 #include "estimator.h"
+#include <cassert>
+#include <climits>
+#include "utils.h"
+#include "prosac.h"
 #include "threading.h"
 #include "utils.h"
 
@@ -221,6 +225,21 @@ void ref_direct_solve(const LineSegment * lines, int n, const int * idx, int n_i
     Eigen::ArrayXi indices = Eigen::Map<const Eigen::ArrayXi>(idx, n_idx);
     DirectEstimator<LinePencilModel> est;
     Eigen::Vector3f r = est.solve(model, indices, 0.f);
+    out3[0] = r.x(); out3[1] = r.y(); out3[2] = r.z();
+}
+
+/* PROSAC_Estimator<LinePencilModel>::solve (reference src/prosac.h:104-299), instantiated here; its generator is seeded through
+ * the std::random_device shim (oracle/seed_shim.h), i.e. with oracle_ref_seed_value */
+void ref_prosac_solve(const LineSegment * lines, int n, const int * idx, int n_idx, float tol, float * out3, int * /*trace: none*/)
+{
+    std::vector<LineSegment> v(lines, lines + n);
+    auto bb = bounding_box(v);
+    Eigen::Vector2f p = bbox_center(bb);
+    float s = bbox_size(bb).maxCoeff();
+    LinePencilModel model(normalize_lines(v, p, s));
+    Eigen::ArrayXi indices = Eigen::Map<const Eigen::ArrayXi>(idx, n_idx);
+    PROSAC_Estimator<LinePencilModel> est;
+    Eigen::Vector3f r = est.solve(model, indices, tol);
     out3[0] = r.x(); out3[1] = r.y(); out3[2] = r.z();
 }
 
