@@ -202,6 +202,15 @@ LRB_API int lrb_assign_to_group_device(lrb_engine * e, const lrb_segment * lines
 LRB_API int lrb_direct_estimate(lrb_engine * e, const lrb_segment * lines, int n_lines, const int * idx, int n_idx,
                                 float * weights, int * cell2, float * vp3);
 
+/* PROSAC_Estimator<LinePencilModel>::solve (reference src/prosac.h:104-299; dormant in the reference like the estimator above): the
+ * listed observations ordered by their Hough weight, at most nine progressively sampled hypotheses scored against all of them,
+ * the reference's stopping rule, fit_optimal on the winner's inliers.  tol: inlier threshold on the line error (reference:
+ * 1 - cos(2 deg)).  The generator is the engine's uniform stream (lrb_set_seed).  Needs 12 <= observations <= 46340 (below, the
+ * reference reads past its list; above, its int products overflow).  vp3: unit vector in normalised coordinates;
+ * trace31 (or NULL): iterations, final n, n*, best inlier count, 9 x 2 sample positions, 9 inlier counts (-1: sample rejected). */
+LRB_API int lrb_prosac_estimate(lrb_engine * e, const lrb_segment * lines, int n_lines, const int * idx, int n_idx, float tol,
+                                float * vp3, int * trace31);
+
 /* ---- stage window (parity tests): contents of slot `slot` after the last lrb_detect_* call on this engine --------- */
 enum lrb_stage {
     LRB_ST_DX = 0, LRB_ST_DY, LRB_ST_MAG,        /* float32 [h*w] */

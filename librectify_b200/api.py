@@ -90,6 +90,7 @@ def load_library(path: str | None = None):
     lib.lrb_warp_perspective_u8.argtypes = [vp, vp, ip, ip, ip, ip, ll, vp, ip, vp, ip, ip, ip, ll]
     lib.lrb_autorectify_u8.argtypes = [vp, vp, ip, ip, ip, ll, fp, ip, vp, fp, vp, vp, ip, C.POINTER(ip), vp, C.c_size_t, C.POINTER(ip), C.POINTER(ip)]
     lib.lrb_direct_estimate.argtypes = [vp, vp, ip, vp, ip, vp, vp, vp]
+    lib.lrb_prosac_estimate.argtypes = [vp, vp, ip, vp, ip, fp, vp, vp]
     lib.lrb_fit_vanishing_point_device.argtypes = [vp, vp, ip, ip, vp]
     lib.lrb_assign_to_group_device.argtypes = [vp, vp, ip, vp, ip, fp]
     lib.lrb_stage_fetch.argtypes = [vp, ip, ip, vp, C.c_size_t]; lib.lrb_stage_fetch.restype = ll
@@ -372,6 +373,16 @@ class Engine:
             shape = (wh.value, ww.value) if a.ndim == 2 else (wh.value, ww.value, ch)
             warped = buf[: wh.value * ww.value * ch].reshape(shape).copy()
         return warped, tf[0], lines[: min(n.value, cap)].copy()
+
+    def prosac_estimate(self, lines: np.ndarray, idx: np.ndarray | None, tol: float):
+        """The reference's dormant PROSAC estimator (src/prosac.h:104-299) on the device. Returns (vanishing point[3], trace dict)."""
+        ln = np.ascontiguousarray(lines, SEG_DTYPE)
+        ix = None if idx is None else np.ascontiguousarray(idx, np.int32)
+        vp = np.zeros(3, np.float32); tr = np.zeros(31, np.int32)
+        self._check(self.lib.lrb_prosac_estimate(self.h, ln.ctypes.data, len(ln), None if ix is None else ix.ctypes.data,
+                                                 0 if ix is None else len(ix), C.c_float(tol), vp.ctypes.data, tr.ctypes.data))
+        return vp, dict(iterations=int(tr[0]), n_final=int(tr[1]), n_star=int(tr[2]), I_N_best=int(tr[3]),
+                        samples=tr[4:22].reshape(9, 2).copy(), I_N=tr[22:31].copy())
 
     def fit_vanishing_point(self, lines: np.ndarray, group: int):
         """fit_vanishing_point (reference src/interface.cpp:211-215) computed on the device"""

@@ -17,7 +17,7 @@ OBJ = os.path.join(HERE, "_obj")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "librectify_b200.so")
 
-CU = ["k1_grad.cu", "k2_nms.cu", "k3_replay.cu", "k4_flood.cu", "k5_fit.cu", "k_refine.cu", "k_warp.cu", "k_hough.cu", "k_aux.cu", "k6_ransac.cu", "k7_sampler.cu", "mt_stream.cu", "ubench.cu", "engine.cu"]
+CU = ["k1_grad.cu", "k2_nms.cu", "k3_replay.cu", "k4_flood.cu", "k5_fit.cu", "k_refine.cu", "k_warp.cu", "k_hough.cu", "k_prosac.cu", "k_aux.cu", "k6_ransac.cu", "k7_sampler.cu", "mt_stream.cu", "ubench.cu", "engine.cu"]
 CPP = ["transform_host.cpp", "api.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 COMMON = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a", "-fmad=false",

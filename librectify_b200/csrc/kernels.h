@@ -62,6 +62,11 @@ void launch_aux_model(const float * seg7, int n, unsigned * box4, float * h, flo
 void launch_aux_common_points(const float * seg7, int n, const float * h, const float * len, const float * norm3,
                               const int * groups, int n_groups, bool all, float * out, cudaStream_t st);
 void launch_aux_assign(float * fresh7, int n_fresh, const int * groups, const float * vps, int n_groups, float thr, cudaStream_t st);
+// k_prosac.cu: PROSAC_Estimator::solve (reference src/prosac.h:104-299) on a model + weights left on the device by launch_hough_direct
+size_t prosac_out_bytes();
+void launch_prosac(const float * h, const float * anchor, const float * dir, const float * len, int n_lines, const int * idx, int m,
+                   const float * weights, const unsigned * stream, unsigned long long stream_len, float tol,
+                   int * sidx, unsigned char * flags, int * inl, void * out, cudaStream_t st);
 // k_warp.cu
 struct WarpMatrix { double m[9]; };    // destination -> source map, row-major (what cv::warpPerspective uses after inverting H)
 void launch_warp_perspective_u8(const unsigned char * src, int sw, int sh, long long spitch, int channels, unsigned char * dst, int dw, int dh,
