@@ -36,12 +36,14 @@ METRIC = "1080p images/sec (detect+VP+transform)"
 K1_BYTES_PER_PX = 17.0          # 4 B read (image) + 8 B (dx, dy) + 4 B (mag) + 1 B (bin) written     
 K2_BYTES_PER_PX = 6.0           # 4 B (mag) + 1 B (bin) read, 1 B (mask8) written
 K8_FLOP_PER_PAIR = 16.0         # flops of the reference's formula per (hypothesis, segment) pair
-# DRAM traffic of K1 from the tracked ncu capture (profiles/r1_ncu_full_final.md: dram__bytes_read.sum + dram__bytes_write.sum of one
-# 8-frame launch = 66.38 + 156.15 MB); not measured in this run — stores still in L2 at kernel end are not counted by ncu
-K1_NCU_DRAM_BYTES_PER_PX = (66.38e6 + 156.15e6) / (8 * 1920 * 1080)
-# warp instructions the flood kernels issue per 1080p frame, from the tracked ncu capture named in FLOOD_INSTR_SOURCE
-FLOOD_WARP_INSTR_PER_FRAME = None
-FLOOD_INSTR_SOURCE = "profiles/ (no capture of the current flood kernels yet)"
+# DRAM traffic of K1 / K2 from the tracked ncu capture profiles/r2_ncu_full_stencils_seeds.md (dram__bytes_read.sum + dram__bytes_write.sum
+# of one 32-frame launch: K1 265.4 + 802.4 MB, K2 332.6 + 61.2 MB); constants of that capture, not measured in this run
+K1_NCU_DRAM_BYTES_PER_PX = (265.444e6 + 802.417e6) / (32 * 1920 * 1080)
+K2_NCU_DRAM_BYTES_PER_PX = (332.646e6 + 61.236e6) / (32 * 1920 * 1080)
+# warp instructions the flood kernels (prune + sub-warp + full-tile + verify, all rounds) issue per 1080p frame: smsp__inst_executed.sum
+# over every flood launch of one 32-frame group, from the tracked launch list named in FLOOD_INSTR_SOURCE
+FLOOD_WARP_INSTR_PER_FRAME = 45.6e6
+FLOOD_INSTR_SOURCE = "profiles/r2_launches_final.md (ncu smsp__inst_executed.sum, 1461 M per 32-frame group)"
 
 
 def measured_peaks():
@@ -364,8 +366,9 @@ def run_b200(args):
         return e
 
     k1 = hbm_entry("k_grad5x5_bin (K1)", "grad", K1_BYTES_PER_PX, K1_NCU_DRAM_BYTES_PER_PX * px * fpl)
-    k1["traffic_source"] = "constant from the tracked ncu capture profiles/r1_ncu_full_final.md (13.4 B/px), scaled to this launch size; not measured in this run"
-    k2 = hbm_entry("k_nms5x5_seeds (K2)", "nms", K2_BYTES_PER_PX)
+    k1["traffic_source"] = "constant from the tracked ncu capture profiles/r2_ncu_full_stencils_seeds.md (16.1 B/px), scaled to this launch size; not measured in this run"
+    k2 = hbm_entry("k_nms5x5_seeds (K2)", "nms", K2_BYTES_PER_PX, K2_NCU_DRAM_BYTES_PER_PX * px * fpl)
+    k2["traffic_source"] = "constant from the same capture (5.9 B/px)"
     stages = {"K1_grad": k1, "K2_nms": k2}
     if fp32:
         # "score" = CUDA events around the k_score launches of the <= 4 solves (a sub-interval of the RANSAC stage)
@@ -390,6 +393,9 @@ def run_b200(args):
         slots_per_s = 148 * 4 * sm_mhz * 1e6
         flood["achieved"] = FLOOD_WARP_INSTR_PER_FRAME / (alone["flood"] * 1e-3) / slots_per_s
         flood["peak"] = 1.0; flood["frac"] = flood["achieved"]
+        flood["note"] = ("issue-slot fraction of the flood stage with ONE engine on the GPU = warp instructions per frame / (148 SMs x 4 schedulers x "
+                         "SM clock x stage time per frame); with four engines the stage intervals overlap other engines' kernels, so no in-bench "
+                         "fraction is given")
     stages["K4_flood"] = flood
     stage_sum = sum(v for k, v in st_bench.items() if k in api.STAGE_TIMERS)
     share = {k: v / max(stage_sum, 1e-12) for k, v in st_bench.items() if k in api.STAGE_TIMERS}
