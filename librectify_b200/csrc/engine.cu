@@ -429,11 +429,16 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     }
     stage(LRB_T_NMS);
     launch_nms(e->tm_mag, e->tm_bin, e->P, e->S, e->ctrl, n, kMarginX, kMarginY, e->st);
+    // Window schedule of the flood: a large batch starts with a small window that doubles (fewer redundant floods of the same long
+    // line: throughput); one or two frames are latency-bound, every extra round is four dependent launches, so they start at the
+    // steady size (three rounds fewer).  The result does not depend on the schedule.
+    Seeds Sg = e->S;
+    if (n <= 2 && !getenv("LRB_WINDOW_FIRST")) Sg.win_first = 1 << 24;
     stage(LRB_T_SEEDS);
-    launch_seed_order(e->P, e->S, e->ctrl, n, e->S.cap, e->st);
+    launch_seed_order(e->P, Sg, e->ctrl, n, e->S.cap, e->st);
     stage(LRB_T_FLOOD);
-    int rounds = kInitialRounds;
-    e->kernels += launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
+    int rounds = (n <= 2) ? 16 : kInitialRounds;
+    e->kernels += launch_flood_rounds(e->P, Sg, e->K, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
     e->kernels += 2 + 1 + 3;
     if (debug_sync) {
         stage(LRB_T_FIT); launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds, e->st);
@@ -478,7 +483,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         if (!more_rounds && !serial && !more_stream) break;
         if (more_rounds && !serial) {
             if (rounds + 16 <= kMaxRounds) {
-                e->kernels += launch_flood_rounds(e->P, e->S, e->K, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
+                e->kernels += launch_flood_rounds(e->P, Sg, e->K, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
                 rounds += 16;
             } else serial = true;
         }

@@ -674,7 +674,8 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         const int firstf = atomicMin(&C.win_first, 0x7fffffff);
         // seeds flooded per round: small at first — the strongest seeds own the long lines, and every other seed on such a line
         // would flood the whole line again, only to lose against the line's strongest seed — then doubling up to the steady size
-        const int budget = min(max(S.win_min, n / S.win_div), S.win_first << min(round + 1, 16));
+        const long long grown = (long long)S.win_first << min(round + 1, 16);
+        const int budget = (int)min((long long)max(S.win_min, n / S.win_div), grown);
         const int nlo = failed ? min(firstf, hi) : hi;
         const int nhi = min(n, hi + max(0, budget - failed));
         C.win_lo = nlo; C.win_hi = nhi;

@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_link(Lines L, FrameCtrl * ct
 }
 
 // ---- phase 3: follow the links from worker 0 and emit the first T samples in chain order -----------------------------------
-__global__ void __launch_bounds__(256) k_sampler_stitch(Lines L, FrameCtrl * ctrl, int solve, int T)
+__global__ void __launch_bounds__(1024) k_sampler_stitch(Lines L, FrameCtrl * ctrl, int solve, int T)
 {
     __shared__ int s_w[kSampWorkers], s_b[kSampWorkers], s_c[kSampWorkers], s_off[kSampWorkers];
     __shared__ int s_n, s_total;
@@ -244,7 +244,7 @@ void launch_sampler(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsign
     LRB_CARVEOUT(k_sampler_segments); LRB_CARVEOUT(k_sampler_link); LRB_CARVEOUT(k_sampler_stitch); LRB_CARVEOUT(k_sampler_tail);
     k_sampler_segments<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
     k_sampler_link<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
-    k_sampler_stitch<<<n_slots, 256, 0, st>>>(L, ctrl, solve, T);
+    k_sampler_stitch<<<n_slots, 1024, 0, st>>>(L, ctrl, solve, T);
     k_sampler_tail<<<n_slots, 32, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
 }
 

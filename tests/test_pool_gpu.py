@@ -16,6 +16,14 @@ def _frames(n):
     return np.stack([manhattan_frame(300 + i, W, H, n_lines=30).numpy() for i in range(n)])
 
 
+RESULT_FIELDS = ["n_lines", "n_seeds", "n_components", "n_pixels", "n_solves", "n_obs", "max_magnitude", "flood_fallback"]
+
+
+def _same_info(a, b):
+    """results identical; the flood statistics (rounds, floods per pass) depend on the launch-group size by design (window schedule)"""
+    return all(np.array_equal(a[f], b[f]) for f in RESULT_FIELDS)
+
+
 def test_pool_matches_single_engine():
     import torch
     from librectify_b200 import api
@@ -27,7 +35,7 @@ def test_pool_matches_single_engine():
     devices = [0, 1] if torch.cuda.device_count() >= 2 else [0, 0]
     pool = api.Pool(devices, engines_per_device=2, slots=2)              # 11 frames over 2 x 2 engines x 2 slots: ragged shards
     tf, info = pool.rectify_host(frames, ML, cfgs)
-    assert tf.tobytes() == tf_ref.tobytes() and info.tobytes() == info_ref.tobytes()
+    assert tf.tobytes() == tf_ref.tobytes() and _same_info(info, info_ref)
     tf2, _ = pool.rectify_host(frames, ML, cfgs, passes=3)
     assert tf2.tobytes() == tf_ref.tobytes()
     u8 = (frames * 256.0).clip(0, 255).astype(np.uint8)
@@ -40,7 +48,7 @@ def test_pool_matches_single_engine():
     lo = len(frames) * 1 // 2
     shards = [torch.from_numpy(frames[:lo]).cuda(devices[0]), torch.from_numpy(frames[lo:]).cuda(devices[1])]
     tfd, infod = pool.rectify_device(shards, ML, cfgs)
-    assert tfd.tobytes() == tf_ref.tobytes() and infod.tobytes() == info_ref.tobytes()
+    assert tfd.tobytes() == tf_ref.tobytes() and _same_info(infod, info_ref)
     pool.close()
 
 
