@@ -51,6 +51,8 @@ typedef struct lrb_frame_info {
     int floods_small;     /* tentative floods finished inside the 8-lane (256-pixel) window of k_flood_small, all rounds */
     int floods_mid;       /* ... inside the 16-lane (512-pixel) window of the second pass */
     int floods_escalated; /* tentative floods handed on to the full-tile path */
+    int n_tied;           /* seeds whose magnitude equals another seed's exactly (their order comes from the std::sort replay) */
+    int replay_steps;     /* partition steps replayed for that (k3_replay.cu) */
 } lrb_frame_info;
 
 typedef struct lrb_engine lrb_engine;

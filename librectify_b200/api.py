@@ -30,8 +30,8 @@ CFG_DTYPE = np.dtype([("vertical_vp_angular_tolerance", "<f4"), ("vertical_vp_mi
                       ("horizontal_vp_min_distance", "<f4"), ("h_strategy", "<i4")])
 INFO_DTYPE = np.dtype([("n_lines", "<i4"), ("n_seeds", "<i4"), ("n_components", "<i4"), ("n_pixels", "<i4"),
                        ("flood_rounds", "<i4"), ("flood_fallback", "<i4"), ("n_solves", "<i4"), ("n_obs", "<i4", 4),
-                       ("max_magnitude", "<f4"), ("floods_small", "<i4"), ("floods_mid", "<i4"), ("floods_escalated", "<i4")])
-assert SEG_DTYPE.itemsize == 28 and TF_DTYPE.itemsize == 80 and CFG_DTYPE.itemsize == 20 and INFO_DTYPE.itemsize == 60
+                       ("max_magnitude", "<f4"), ("floods_small", "<i4"), ("floods_mid", "<i4"), ("floods_escalated", "<i4"), ("n_tied", "<i4"), ("replay_steps", "<i4")])
+assert SEG_DTYPE.itemsize == 28 and TF_DTYPE.itemsize == 80 and CFG_DTYPE.itemsize == 20 and INFO_DTYPE.itemsize == 68
 
 STAGES = dict(dx=0, dy=1, mag=2, bin=3, mask8=4, seeds=5, labels=6, comp_sizes=7, raw_segs=8, model_h=9, model_anchor=10,
               model_dir=11, model_len=12, model_bbox=13, pairs=14, scores=15, ransac=16, stream=17, refined_segs=18)

@@ -516,6 +516,7 @@ void fill_info(const lrb_engine * e, int i, lrb_frame_info * out)
     for (int k = 0; k < 4; ++k) out->n_obs[k] = k < C.n_solves ? C.n_obs[k] : 0;
     unsigned g = C.gmax_bits; float f; memcpy(&f, &g, 4); out->max_magnitude = f;
     out->floods_small = C.floods_small; out->floods_mid = C.floods_mid; out->floods_escalated = C.floods_esc;
+    out->n_tied = C.n_tied; out->replay_steps = C.replay_steps;
 }
 
 int detect(lrb_engine * e, const float * frames, bool on_device, int n_frames, int w, int h, long long pitch,

@@ -244,14 +244,19 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
                 // right stoppers of this slice that lie right of element i = (all of the slice) - (those up to and including i)
                 const int slice_r = (warp == 0 ? A.totR[s] : A.cntR[s][warp - 1]) - A.cntR[s][warp];
                 int br = A.cntR[s][warp] + slice_r;                                      // index of a right stopper = br - (right stoppers of the slice up to and including it)
-                for (int base = i0; base < i1; base += 32) {
-                    const int i = base + lane;
-                    const unsigned k = i < i1 ? a[i].x : 0u;
-                    const bool fL = i < i1 && !rp_before(k, pv), fR = i < i1 && !rp_before(pv, k);
-                    const unsigned bL = __ballot_sync(0xffffffffu, fL), bR = __ballot_sync(0xffffffffu, fR);
-                    if (fL) Lp[f + 1 + bl + __popc(bL & lt)] = i;
-                    if (fR) Rp[f + 1 + br - 1 - __popc(bR & lt)] = i;
-                    bl += __popc(bL); br -= __popc(bR);
+                for (int base0 = i0; base0 < i1; base0 += 128) {             // four chunks of keys in flight per round trip
+                    unsigned kk[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { const int i = base0 + 32 * u + lane; kk[u] = i < i1 ? a[i].x : 0u; }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int i = base0 + 32 * u + lane;
+                        const bool fL = i < i1 && !rp_before(kk[u], pv), fR = i < i1 && !rp_before(pv, kk[u]);
+                        const unsigned bL = __ballot_sync(0xffffffffu, fL), bR = __ballot_sync(0xffffffffu, fR);
+                        if (fL) Lp[f + 1 + bl + __popc(bL & lt)] = i;
+                        if (fR) Rp[f + 1 + br - 1 - __popc(bR & lt)] = i;
+                        bl += __popc(bL); br -= __popc(bR);
+                    }
                 }
             }
             __syncthreads();
@@ -260,13 +265,22 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
                 const int f = A.seg[s].x, l = A.seg[s].y;
                 if (l <= f) continue;
                 const int mn = min(A.totL[s], A.totR[s]);
-                for (int k = tid; k < mn; k += RP_THREADS) {
-                    const int lp = Lp[f + 1 + k], rp = Rp[f + 1 + k];
-                    const bool sw = lp < rp;
-                    if (sw) {
-                        const uint2 x = a[lp], y = a[rp]; a[lp] = y; a[rp] = x;
-                        const bool nxt = (k + 1 < mn) && (Lp[f + 2 + k] < Rp[f + 2 + k]);
-                        if (!nxt) A.K[s] = k + 1;
+                for (int k0 = tid; k0 < mn; k0 += 4 * RP_THREADS) {            // four independent exchanges per thread in flight
+                    int lp[4], rp[4], ln[4], rn[4]; bool sw[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int k = k0 + u * RP_THREADS; const bool ok = k < mn, okn = k + 1 < mn;
+                        lp[u] = ok ? Lp[f + 1 + k] : 0; rp[u] = ok ? Rp[f + 1 + k] : 0;
+                        ln[u] = okn ? Lp[f + 2 + k] : 1; rn[u] = okn ? Rp[f + 2 + k] : 0;
+                        sw[u] = ok && lp[u] < rp[u];
+                    }
+                    uint2 x[4], y[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) if (sw[u]) { x[u] = a[lp[u]]; y[u] = a[rp[u]]; }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) if (sw[u]) {
+                        a[lp[u]] = y[u]; a[rp[u]] = x[u];
+                        if (!(ln[u] < rn[u])) A.K[s] = k0 + u * RP_THREADS + 1;  // the last exchange of the prefix
                     }
                 }
             }
@@ -289,6 +303,7 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
                 const bool left_small = (cut - f) <= (l - cut);
                 const int s0 = left_small ? f : cut, s1 = left_small ? cut : l;
                 int cnt = 0;
+#pragma unroll 4
                 for (int i = s0 + tid; i < s1; i += RP_THREADS) cnt += (a[i].y & kTiedBit) ? 1 : 0;
                 if (__any_sync(0xffffffffu, cnt != 0)) {
 #pragma unroll
@@ -368,10 +383,12 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
     if (!fixup) return;
     // ---- final order: stable by key of the arrangement above.  Only tied peaks move, inside their group's rank range. ----
     // (1) position of every rank
+#pragma unroll 4
     for (int p = tid; p < n; p += RP_THREADS) Lp[a[p].y & ~kTiedBit] = p;
     __syncthreads();
     // (2) final rank of a tied peak = first rank of its group + members of the group left of it; remember its pixel
     unsigned * sidx = S.idx + so;
+#pragma unroll 4
     for (int p = tid; p < n; p += RP_THREADS) {
         const uint2 el = a[p];
         if (!(el.y & kTiedBit)) continue;
@@ -385,6 +402,7 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
         Rp[rank] = (int)el.x + before;
     }
     __syncthreads();
+#pragma unroll 4
     for (int p = tid; p < n; p += RP_THREADS) {                            // Lp is free again: park the pixel of every tied rank
         const uint2 el = a[p];
         if (el.y & kTiedBit) { const int rank = (int)(el.y & ~kTiedBit); Lp[rank] = (int)sidx[rank]; }
@@ -392,6 +410,7 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
     __syncthreads();
     // (3) move the per-seed records (pixel, bin, flood threshold; the other per-seed arrays still hold their initial values)
     const size_t pbase = (size_t)slot * P.stride;
+#pragma unroll 4
     for (int p = tid; p < n; p += RP_THREADS) {
         const uint2 el = a[p];
         if (!(el.y & kTiedBit)) continue;
