@@ -195,6 +195,21 @@ LRB_API int lrb_fit_vanishing_point_device(lrb_engine * e, const lrb_segment * l
 LRB_API int lrb_assign_to_group_device(lrb_engine * e, const lrb_segment * lines, int n_lines, lrb_segment * new_lines, int n_new_lines,
                                        float angular_tolerance_deg);
 
+/* fit_vanishing_point for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same kernels and
+ * bit-identical result as lrb_fit_vanishing_point_device, but
+ *   - d_lines (n_lines segments) and d_out (one lrb_point) are DEVICE memory of `device`, provided by the caller;
+ *   - the scratch (model of the lines: 16 bytes per line + 768) is a static __device__ array inside the library, sized for
+ *     LRB_NOALLOC_MAX_LINES lines (1 MiB + 768 B, held by every GPU that loads the library until exit); more lines: error -5;
+ *   - the call makes `device` current, enqueues four kernels on `stream` (a cudaStream_t of that device, NULL = default stream)
+ *     and returns without synchronising: d_out is valid once the stream has passed them.  It calls no cudaMalloc / cudaFree or
+ *     any allocating routine and needs no engine.
+ * Every call on a device shares the one scratch array (it is re-initialised on the stream by each call): calls that overlap
+ * on the GPU - different streams without an ordering between them - race; calls on one stream are safe. */
+#define LRB_NOALLOC_MAX_LINES 65536
+LRB_API int lrb_fit_vanishing_point_noalloc(int device, const lrb_segment * d_lines, int n_lines, int group, lrb_point * d_out,
+                                            void * stream);
+
 /* ---- the reference's dormant Hough-voted estimator ---------------------------------------------
  * LinePencilModel::get_weights (reference src/line_pencil.cpp:47-86: 20 000 pair intersections voted into a 65 x 65
  * accumulator, weight = inclination^4 towards the winning cell's direction) and DirectEstimator::solve (reference

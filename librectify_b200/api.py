@@ -93,6 +93,7 @@ def load_library(path: str | None = None):
     lib.lrb_prosac_estimate.argtypes = [vp, vp, ip, vp, ip, fp, vp, vp]
     lib.lrb_fit_vanishing_point_device.argtypes = [vp, vp, ip, ip, vp]
     lib.lrb_assign_to_group_device.argtypes = [vp, vp, ip, vp, ip, fp]
+    lib.lrb_fit_vanishing_point_noalloc.argtypes = [ip, vp, ip, ip, vp, vp]
     lib.lrb_stage_fetch.argtypes = [vp, ip, ip, vp, C.c_size_t]; lib.lrb_stage_fetch.restype = ll
     lib.lrb_profile_enable.argtypes = [vp, ip]; lib.lrb_profile_enable.restype = None
     lib.lrb_profile_reset.argtypes = [vp]; lib.lrb_profile_reset.restype = None

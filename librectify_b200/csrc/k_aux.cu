@@ -8,6 +8,9 @@
 // results are bit-identical to them: the model (bounding box, normalised homogeneous lines, lengths) is built one thread per
 // line, the 3x3 scatter of a group is six sequential running sums (one lane each, members in index order), the eigenvector comes
 // from the shared Eigen-convention solver, and the assignment is one thread per new line looping over the groups in ascending id.
+#include <cstdio>
+#include <mutex>
+
 #include "common.cuh"
 #include "eig.cuh"
 #include "kernels.h"
@@ -150,6 +153,67 @@ void launch_aux_common_points(const float * seg7, int n, const float * h, const 
 void launch_aux_assign(float * fresh7, int n_fresh, const int * groups, const float * vps, int n_groups, float thr, cudaStream_t st)
 {
     k_aux_assign<<<(n_fresh + 255) / 256, 256, 0, st>>>(reinterpret_cast<SegRec *>(fresh7), n_fresh, groups, vps, n_groups, thr);
+}
+
+
+// ---- allocation-free variant of fit_vanishing_point (lrb_fit_vanishing_point_noalloc) ------------------------------------------
+// No counterpart in the reference: for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  Same kernels as launch_aux_model + launch_aux_common_points; the scratch they need (bounding box,
+// normalisation, group id, h and len of the model) lives in ONE file-scope device array that every device loading the library
+// holds until exit: kAuxNoAllocScratchBytes = 768 + 16 * kAuxNoAllocMaxLines = 1 MiB + 768 B.  All calls on a device share it
+// and it keeps the last call's contents: the bounding box is re-initialised on the stream by every call, h / len / norm3 / group
+// id are overwritten for the lines of the call before they are read.  Calls that overlap on the GPU (two streams) race.
+namespace {
+
+constexpr size_t kNaBox = 0, kNaNorm = 256, kNaGroup = 512, kNaH = 768;
+constexpr size_t kNaLen = kNaH + 12 * (size_t)kAuxNoAllocMaxLines;
+constexpr size_t kAuxNoAllocScratchBytes = kNaLen + 4 * (size_t)kAuxNoAllocMaxLines;
+
+static __device__ __align__(256) unsigned char g_aux_noalloc_scratch[kAuxNoAllocScratchBytes];
+
+constexpr int kNaMaxDevices = 64;
+unsigned char * g_na_ptr[kNaMaxDevices];      // device address of the array above, per device (the symbol itself is a host-side stand-in)
+std::mutex g_na_mutex;
+
+// what must not carry over from the previous call: min / max identities of the bounding box; and the group id of this call
+__global__ void k_aux_noalloc_init(unsigned * box, int * groups, int group)
+{
+    box[0] = 0xFFFFFFFFu; box[1] = 0xFFFFFFFFu; box[2] = 0u; box[3] = 0u;
+    groups[0] = group;
+}
+
+} // namespace
+
+int aux_fit_vanishing_point_noalloc(int device, const float * d_seg7, int n, int group, float * d_out3, cudaStream_t st,
+                                    char * err, size_t err_len)
+{
+#define NA_CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { snprintf(err, err_len, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); return -2; } } while (0)
+    if (device < 0 || device >= kNaMaxDevices) { snprintf(err, err_len, "device %d out of range", device); return -1; }
+    NA_CK(cudaSetDevice(device));
+    unsigned char * base;
+    {   // set-up, once per device, with that device current
+        std::lock_guard<std::mutex> lock(g_na_mutex);
+        if (!g_na_ptr[device]) {
+            void * p = nullptr;
+            NA_CK(cudaGetSymbolAddress(&p, g_aux_noalloc_scratch));
+            g_na_ptr[device] = static_cast<unsigned char *>(p);
+        }
+        base = g_na_ptr[device];
+    }
+    unsigned * box = reinterpret_cast<unsigned *>(base + kNaBox);
+    float * norm3 = reinterpret_cast<float *>(base + kNaNorm);
+    int * groups = reinterpret_cast<int *>(base + kNaGroup);
+    float * h = reinterpret_cast<float *>(base + kNaH);
+    float * len = reinterpret_cast<float *>(base + kNaLen);
+    const SegRec * seg = reinterpret_cast<const SegRec *>(d_seg7);
+    const int blocks = (n + 255) / 256;
+    k_aux_noalloc_init<<<1, 1, 0, st>>>(box, groups, group);
+    k_aux_bbox<<<blocks < 1184 ? blocks : 1184, 256, 0, st>>>(seg, n, box);
+    k_aux_model<<<blocks, 256, 0, st>>>(seg, n, box, h, len, norm3);
+    k_aux_common_point<<<1, 32, 0, st>>>(seg, n, h, len, norm3, groups, group <= 0 ? 1 : 0, d_out3);
+    NA_CK(cudaGetLastError());
+    return 0;
+#undef NA_CK
 }
 
 } // namespace lrb

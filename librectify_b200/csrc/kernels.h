@@ -62,6 +62,11 @@ void launch_aux_model(const float * seg7, int n, unsigned * box4, float * h, flo
 void launch_aux_common_points(const float * seg7, int n, const float * h, const float * len, const float * norm3,
                               const int * groups, int n_groups, bool all, float * out, cudaStream_t st);
 void launch_aux_assign(float * fresh7, int n_fresh, const int * groups, const float * vps, int n_groups, float thr, cudaStream_t st);
+// allocation-free fit_vanishing_point on device-resident lines: scratch in a static __device__ array of k_aux.cu (<= kAuxNoAllocMaxLines
+// lines); enqueues on `st` and returns; 0, or a negative code with a message in err
+constexpr int kAuxNoAllocMaxLines = 65536;
+int aux_fit_vanishing_point_noalloc(int device, const float * d_seg7, int n, int group, float * d_out3, cudaStream_t st,
+                                    char * err, size_t err_len);
 // k_prosac.cu: PROSAC_Estimator::solve (reference src/prosac.h:104-299) on a model + weights left on the device by launch_hough_direct
 size_t prosac_out_bytes();
 void launch_prosac(const float * h, const float * anchor, const float * dir, const float * len, int n_lines, const int * idx, int m,
