@@ -626,7 +626,7 @@ k_flood_prune(Planes P, Seeds S, FrameCtrl * ctrl, int round, int slot0)
     }
 }
 
-// verify + commit + mark visited, one warp per window seed; the last block to finish moves the window
+// verify + commit + mark visited, eight lanes per window seed; the last block to finish moves the window
 __global__ void __launch_bounds__(256)
 k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned epoch_first, int slot0)
 {
@@ -642,28 +642,39 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
     uint8_t * vis = P.vis + pbase;
     const unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    // eight lanes per seed, four seeds per warp (the typical region has 6 pixels: profiles/r2_flood_regions.md); four list entries
+    // per lane in flight so that a long region still costs size / 32 dependent round trips
+    const int sub = lane & 7, grp = lane >> 3;
     int live = 0, first = 0x7fffffff;
-    for (int rank = lo + blockIdx.x * nw + warp; rank < hi; rank += gridDim.x * nw) {
-        if (S.status[so + rank] != kStatusLive) continue;
+    for (int r0 = lo + (blockIdx.x * nw + warp) * 4; r0 < hi; r0 += gridDim.x * nw * 4) {
+        const int rank = r0 + grp;
+        const bool valid = rank < hi && S.status[so + rank] == kStatusLive;
         const unsigned key = (epoch << 24) | (unsigned)rank;
-        const int size = S.size[so + rank];
+        const int size = valid ? S.size[so + rank] : 0;
+        const unsigned * list = pool + (valid ? S.list_head[so + rank] : 0);
         // pass 1: is every pixel still stamped with this seed's key?
-        const unsigned * list = pool + S.list_head[so + rank];
         bool mine = true;
-        for (int i = lane; i < size; i += 32) {
-            const unsigned w = __ldcg(list + i);
-            mine &= (__ldcg(owner + (size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)) == key);
+        for (int i = sub; i < size; i += 32) {
+            unsigned w[4], o[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) w[u] = __ldcg(list + min(i + 8 * u, size - 1));
+#pragma unroll
+            for (int u = 0; u < 4; ++u) o[u] = __ldcg(owner + (size_t)(w[u] >> 16) * P.pitch + (w[u] & 0xFFFFu));
+#pragma unroll
+            for (int u = 0; u < 4; ++u) mine &= (o[u] == key);
         }
-        mine = __all_sync(0xffffffffu, mine);
-        if (!mine) { ++live; first = min(first, rank); continue; }
+        const unsigned bm = __ballot_sync(0xffffffffu, mine);
+        if (!valid) continue;
+        if (((bm >> (8 * grp)) & 0xFFu) != 0xFFu) { ++live; first = min(first, rank); continue; }
         // pass 2: the region is final — it becomes part of the visited mask (whether or not it is kept later)
-        for (int i = lane; i < size; i += 32) {
+        for (int i = sub; i < size; i += 8) {
             const unsigned w = __ldcg(list + i);
             vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
         }
-        if (lane == 0) S.status[so + rank] = key;
+        if (sub == 0) S.status[so + rank] = key;
     }
-    if (lane == 0 && live) { atomicAdd(&C.win_live, live); atomicMin(&C.win_first, first); }
+    if (sub != 0) live = 0;
+    if (live) { atomicAdd(&C.win_live, live); atomicMin(&C.win_first, first); }
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) s_last = (atomicAdd(&C.win_blocks, 1) == (int)gridDim.x - 1);

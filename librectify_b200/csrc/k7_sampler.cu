@@ -30,40 +30,49 @@ constexpr int SMP_AHEAD = 8;        // 32-position chunks kept in flight per war
 
 // Walk the chain from sample start `o`, calling f(start, s0, s1, next_start) after every completed sample (warp-uniform
 // arguments); stops when f returns false.  Returns false if the stream ran out.
+// The loop runs on 32-bit stream positions (the stream has 2^25 entries) and decides a chunk of 32 positions with one high
+// multiply per lane: (n - t) * k < (2 - m) * 2^32  <=>  umulhi(n - t, k) < 2 - m  (n - t < 2^31, k < 2^32; exact).  Lanes past the
+// end of a sample (t >= n, where n - t wraps) cannot be mistaken for a pick: Algorithm S is forced to pick at n - t == 2 - m, so a
+// legitimate pick always lies at an earlier lane and the first set bit of the ballot is taken.  12 instructions per chunk instead
+// of the 45 of the 64-bit form (profiles/r2_launches_final.md: the sampler was 20 M of a frame's 115 M warp instructions).
 template <class F>
-__device__ __forceinline__ bool chain_walk(const unsigned * __restrict__ stream, unsigned long long stream_len, long long n,
-                                           unsigned long long o, F f)
+__device__ __forceinline__ bool chain_walk(const unsigned * __restrict__ stream, unsigned long long stream_len, long long n_ll,
+                                           unsigned long long o_ull, F f)
 {
-    const int lane = threadIdx.x & 31;
-    unsigned long long cur = o;                     // first unconsumed stream position
-    unsigned long long base = o & ~31ull;
-    int m = 0, s0 = 0;
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned len = (unsigned)min(stream_len, 0xFFFFFF00ull);
+    if (o_ull >= len) return false;
+    const unsigned n = (unsigned)n_ll, last = len - 1;
+    unsigned o = (unsigned)o_ull;                   // start of the current sample
+    unsigned cur = o;                               // first unconsumed stream position
+    unsigned base = o & ~31u;
+    unsigned no = n + o;                            // n - t = no - p for position p
+    unsigned lim = 2;                               // 2 - m
+    int s0 = 0;
     unsigned kk[SMP_AHEAD];
 #pragma unroll
-    for (int a = 0; a < SMP_AHEAD; ++a) { const unsigned long long p = base + 32ull * a + lane; kk[a] = p < stream_len ? __ldg(stream + p) : 0u; }
+    for (int a = 0; a < SMP_AHEAD; ++a) kk[a] = __ldg(stream + min(base + 32u * a + lane, last));
     while (true) {
 #pragma unroll
         for (int a = 0; a < SMP_AHEAD; ++a) {
             const unsigned k = kk[a];
-            const unsigned long long p = base + lane;
-            if (base + 32 > stream_len) return false;
-            { const unsigned long long pn = p + 32ull * SMP_AHEAD; kk[a] = pn < stream_len ? __ldg(stream + pn) : 0u; }
+            const unsigned p = base + lane;
+            if (base + 32u > len) return false;
+            kk[a] = __ldg(stream + min(p + 32u * SMP_AHEAD, last));
             while (true) {
-                const long long t = (long long)(p - o);                          // draws already made in this sample
-                const bool can = (p >= cur) && (t < n);
-                const bool sel = can && ((unsigned long long)(n - t) * (unsigned long long)k < ((unsigned long long)(2 - m) << 32));
+                const bool sel = (p >= cur) && (__umulhi(no - p, k) < lim);
                 const unsigned bm = __ballot_sync(0xffffffffu, sel);
                 if (bm == 0) break;
-                const unsigned long long pos = base + (__ffs(bm) - 1);
-                if (m == 0) { s0 = (int)(pos - o); m = 1; cur = pos + 1; }
+                const unsigned pos = base + (unsigned)(__ffs(bm) - 1);
+                if (lim == 2) { s0 = (int)(pos - o); lim = 1; cur = pos + 1; }
                 else {
-                    const unsigned long long start = o;
+                    const unsigned start = o;
                     const int s1 = (int)(pos - o);
-                    m = 0; o = pos + 1; cur = o;
-                    if (!f(start, s0, s1, o)) return true;
+                    lim = 2; o = pos + 1; cur = o; no = n + o;
+                    if (!f((unsigned long long)start, s0, s1, (unsigned long long)o)) return true;
                 }
             }
-            base += 32; if (cur < base) cur = base;
+            base += 32u;
         }
     }
 }
