@@ -63,6 +63,7 @@ constexpr int kSeedBuckets = 4096;
 constexpr int kSampWorkers = 128, kSampRecords = 512;
 constexpr int kFloodWindowMin = 4096, kFloodWindowDiv = 6;   // steady window: max(4096, n_seeds / 6) seeds per round ...
 constexpr int kFloodWindowFirst = 256;                       // ... reached by doubling from this size in round 0
+constexpr int kFitSmallMax = 32;                             // components up to this size are fitted by eight lanes (k5_fit.cu)
 
 // ---- per-frame control block (device memory, one per slot; zeroed by k_frame_init) -------------------------------
 constexpr int kMaxRounds = 96;
@@ -89,7 +90,9 @@ struct FrameCtrl {
     int floods_small, floods_mid, floods_esc;   // statistics over all rounds: floods finished in the 8-lane / 16-lane window / handed to the full-tile path
     int esc2_n, esc2_q;        // the same for the second (16-lane) pass -> full-tile path
     int esc_n, esc_q;          // floods of the current round that outgrew the sub-warp window (escalated to the full-tile path), next one handed out
-    int fit_queue;             // next kept component handed out by the fit kernel
+    int fit_queue;             // next entry of the list of large components handed out by the fit kernel (one warp per component)
+    int fit_queue_small;       // next kept component handed out to the sub-warp path (eight lanes per component, four per warp)
+    int n_big;                 // kept components with more than kFitSmallMax pixels (their indices: Seeds::esc, free after the flood)
     int n_edges, n_merged, refine_overflow;   // `refine` post-process (k_refine.cu): collinearity edges, merged segments, edge list full
     // grouping state
     int num_obs;               // reference estimator.h:119

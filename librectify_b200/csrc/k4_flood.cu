@@ -657,9 +657,9 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         for (int i = sub; i < size; i += 32) {
             unsigned w[4], o[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) w[u] = __ldcg(list + min(i + 8 * u, size - 1));
+            for (int u = 0; u < 4; ++u) w[u] = (i + 8 * u < size) ? __ldcg(list + i + 8 * u) : 0u;
 #pragma unroll
-            for (int u = 0; u < 4; ++u) o[u] = __ldcg(owner + (size_t)(w[u] >> 16) * P.pitch + (w[u] & 0xFFFFu));
+            for (int u = 0; u < 4; ++u) o[u] = (i + 8 * u < size) ? __ldcg(owner + (size_t)(w[u] >> 16) * P.pitch + (w[u] & 0xFFFFu)) : key;
 #pragma unroll
             for (int u = 0; u < 4; ++u) mine &= (o[u] == key);
         }

@@ -29,7 +29,7 @@ static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
 __global__ void __launch_bounds__(1024) k_comp_select(Seeds S, Comps K, FrameCtrl * ctrl, int rounds_total)
 {
     __shared__ int wcnt[32], wpx[32];
-    __shared__ int base_c, base_px;
+    __shared__ int base_c, base_px, n_big;
     const int slot = blockIdx.x;
     FrameCtrl & C = ctrl[slot];
     const int n = C.n_seeds;
@@ -38,10 +38,11 @@ __global__ void __launch_bounds__(1024) k_comp_select(Seeds S, Comps K, FrameCtr
     if (C.fit_done) return;                               // repair pass for another slot: this one is already fitted
     // floods not finished (more rounds or the serial fallback needed): publish nothing; the host re-runs from here
     if ((C.live[rounds_total] != 0 && !C.flood_done) || C.flood_overflow) {
-        if (t == 0) { C.n_comp = 0; C.n_px = 0; C.fit_queue = 0; }
+        if (t == 0) { C.n_comp = 0; C.n_px = 0; C.fit_queue = 0; C.fit_queue_small = 0; C.n_big = 0; }
         return;
     }
-    if (t == 0) { base_c = 0; base_px = 0; }
+    int * biglist = S.esc + so;                           // the flood's escalation list is free by now
+    if (t == 0) { base_c = 0; base_px = 0; n_big = 0; }
     __syncthreads();
     for (int i0 = 0; i0 < n; i0 += 1024) {
         const int i = i0 + t;
@@ -73,14 +74,17 @@ __global__ void __launch_bounds__(1024) k_comp_select(Seeds S, Comps K, FrameCtr
         const int cpos = base_c + ic - keep + (warp ? wcnt[warp - 1] : 0);
         const int ppos = base_px + ip - sz + (warp ? wpx[warp - 1] : 0);
         if (keep) {
-            if (cpos < K.cap && ppos + sz <= K.cap_px) { K.rank[ko + cpos] = i; K.off[ko + cpos] = ppos; K.size[ko + cpos] = sz; }
+            if (cpos < K.cap && ppos + sz <= K.cap_px) {
+                K.rank[ko + cpos] = i; K.off[ko + cpos] = ppos; K.size[ko + cpos] = sz;
+                if (sz > kFitSmallMax) biglist[atomicAdd(&n_big, 1)] = cpos;     // any order: every component writes its own segment record
+            }
             else C.comp_overflow = 1;
         }
         __syncthreads();
         if (t == 0) { base_c += wcnt[31]; base_px += wpx[31]; }
         __syncthreads();
     }
-    if (t == 0) { C.n_comp = min(base_c, K.cap); C.n_px = base_px; C.fit_queue = 0; }
+    if (t == 0) { C.n_comp = min(base_c, K.cap); C.n_px = base_px; C.fit_queue = 0; C.fit_queue_small = 0; C.n_big = n_big; }
 }
 
 // running sums evaluated strictly in list order: lanes 0..NS-1 each own one sum; terms come through shared memory
@@ -107,29 +111,34 @@ __device__ __forceinline__ void seq_accumulate(float (*stage)[32], const float (
 __global__ void __launch_bounds__(FIT_WARPS * 32)
 k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
 {
-    __shared__ __align__(16) float stage_all[FIT_WARPS][3][32];
+    // per warp: the large-component path uses stage[3][32], val[FIT_RING], ring[FIT_RING]; the sub-warp path the same memory as
+    // four sets of stage[3][kFitSmallMax], val[kFitSmallMax], ring[kFitSmallMax]
+    __shared__ __align__(16) float stage_all[FIT_WARPS][4 * 3 * kFitSmallMax];
     __shared__ float val_all[FIT_WARPS][FIT_RING];         // weights of a component that fits the ring (no re-reads from global memory)
     __shared__ unsigned ring_all[FIT_WARPS][FIT_RING];     // the last FIT_RING accepted pixels of the walk (the BFS frontier lives here)
+    static_assert(4 * kFitSmallMax <= FIT_RING && 4 * 3 * kFitSmallMax >= 3 * 32, "shared-memory sets of the two paths");
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
     if (C.fit_done) return;
-    const int ncomp = C.n_comp;
+    const int ncomp = C.n_big;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float (*stage)[32] = stage_all[warp];
+    float (*stage)[32] = reinterpret_cast<float (*)[32]>(stage_all[warp]);
     unsigned * ring = ring_all[warp];
     float * vring = val_all[warp];
+    const int * biglist = S.esc + (size_t)slot * S.cap;
     const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap, pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
     const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
 
-    // components are handed out dynamically in seed order (large components tend to come first); the next one is
-    // requested before the current one is walked
+    // ---- large components (more than kFitSmallMax pixels): one warp each, handed out dynamically from the list k_comp_select
+    // made; the next one is requested before the current one is walked.  Every warp starts here, so the long walks start first.
     int nxt = 0;
     if (lane == 0) nxt = atomicAdd(&C.fit_queue, 1);
     while (true) {
-        const int comp = __shfl_sync(0xffffffffu, nxt, 0);
-        if (comp >= ncomp) break;
+        const int bpos = __shfl_sync(0xffffffffu, nxt, 0);
+        if (bpos >= ncomp) break;
         if (lane == 0) nxt = atomicAdd(&C.fit_queue, 1);
+        const int comp = biglist[bpos];
         const int rank = K.rank[ko + comp];
         const int n = K.size[ko + comp];
         unsigned * px = K.px + (size_t)slot * K.cap_px + K.off[ko + comp];
@@ -276,6 +285,143 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
 #undef LRB_VAL
         __syncwarp();
     }
+
+    // ---- small components: eight lanes each, four per warp ---------------------------------------------------------------
+    // The typical component has 10-20 pixels, and its walk has one or two parents per step: a warp per component leaves most
+    // lanes idle.  Here a step pops ONE parent per component and tests its eight neighbours in the reference's order (lane =
+    // neighbour) — literally the sequential flood of src/filter.cpp:123-151 — and the sums run over shared-memory rows with one
+    // lane per running sum, in list order, exactly as above.
+    {
+        const int sub = lane & 7, grp = lane >> 3;
+        const int ncs = C.n_comp;
+        float * sstage = stage_all[warp] + grp * 3 * kFitSmallMax;          // [3][kFitSmallMax]
+        unsigned * sring = ring_all[warp] + grp * kFitSmallMax;
+        float * sval = val_all[warp] + grp * kFitSmallMax;
+        const int ndr = kDr[sub], ndc = kDc[sub];
+        // sequential sum of row `r` (list order), by the lane that calls it
+        auto row_sum = [&](int r, int m) {
+            const float4 * row = reinterpret_cast<const float4 *>(sstage + r * kFitSmallMax);
+            float acc = 0.f;
+            for (int k0 = 0; k0 < m; k0 += 4) {
+                const float4 v = row[k0 >> 2];
+                acc = (k0 == 0) ? v.x : __fadd_rn(acc, v.x);
+                if (k0 + 1 < m) acc = __fadd_rn(acc, v.y);
+                if (k0 + 2 < m) acc = __fadd_rn(acc, v.z);
+                if (k0 + 3 < m) acc = __fadd_rn(acc, v.w);
+            }
+            return acc;
+        };
+        int nx2 = 0;
+        if (lane == 0) nx2 = atomicAdd(&C.fit_queue_small, 4);
+        while (true) {
+            const int c0 = __shfl_sync(0xffffffffu, nx2, 0);
+            if (c0 >= ncs) break;
+            if (lane == 0) nx2 = atomicAdd(&C.fit_queue_small, 4);
+            const int comp = c0 + grp;
+            int n = comp < ncs ? K.size[ko + comp] : 0;
+            if (n > kFitSmallMax) n = 0;                                     // a large one: done above
+            if (!__any_sync(0xffffffffu, n > 0)) continue;
+            const bool on = n > 0;
+            const int rank = on ? K.rank[ko + comp] : 0;
+            unsigned * px = K.px + (size_t)slot * K.cap_px + (on ? K.off[ko + comp] : 0);
+            const unsigned ckey = on ? S.status[so + rank] : 0u;
+            const unsigned listed = 0xFF000000u | (unsigned)rank;
+            const int b = on ? S.bin[so + rank] : 0;
+            const unsigned spx = on ? S.idx[so + rank] : 0u;
+            int head = 0, tail = on ? 1 : 0;
+            if (on && sub == 0) {
+                const int sr = spx / P.w, sc = spx - sr * P.w;
+                const unsigned rc0 = ((unsigned)sr << 16) | (unsigned)sc;
+                __stcg(px, rc0); sring[0] = rc0;
+                __stcg(owner + (size_t)sr * P.pitch + sc, listed);
+            }
+            __syncwarp();
+            while (__any_sync(0xffffffffu, head < tail)) {
+                const bool act = head < tail;
+                const unsigned prc = act ? sring[head] : 0x00010001u;
+                head += act ? 1 : 0;
+                const int r = (int)(prc >> 16) + ndr, c = (int)(prc & 0xFFFFu) + ndc;
+                const size_t po = (size_t)r * P.pitch + c;
+                const unsigned own = act ? __ldcg(owner + po) : 0u;
+                const bool take = act && (own == ckey);
+                const unsigned tm = (__ballot_sync(0xffffffffu, take) >> (8 * grp)) & 0xFFu;
+                if (take) {
+                    const int pos = tail + __popc(tm & ((1u << sub) - 1u));
+                    const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
+                    if (pos < n) { __stcg(px + pos, rcq); sring[pos] = rcq; }
+                    __stcg(owner + po, listed);
+                }
+                tail += __popc(tm);
+                __syncwarp();
+            }
+            const int m = min(tail, n);
+            // pass 1: weights and their sum
+            for (int i = sub; i < m; i += 8) {
+                const unsigned rc = sring[i];
+                const size_t po = (size_t)(rc >> 16) * P.pitch + (rc & 0xFFFFu);
+                const float v = orient_energy(__ldg(dx + po), __ldg(dy + po), b);
+                sval[i] = v; sstage[i] = v;
+            }
+            __syncwarp();
+            float acc = (sub == 0 && m > 0) ? row_sum(0, m) : 0.f;
+            const float wsum = __shfl_sync(0xffffffffu, acc, 0, 8);
+            __syncwarp();
+            // pass 2: weighted mean
+            for (int i = sub; i < m; i += 8) {
+                const unsigned rc = sring[i];
+                const float wt = __fdiv_rn(sval[i], wsum);
+                sstage[i] = __fmul_rn((float)(rc >> 16), wt); sstage[kFitSmallMax + i] = __fmul_rn((float)(rc & 0xFFFFu), wt);
+            }
+            __syncwarp();
+            acc = (sub < 2 && m > 0) ? row_sum(sub, m) : 0.f;
+            const float a0 = __shfl_sync(0xffffffffu, acc, 0, 8), a1 = __shfl_sync(0xffffffffu, acc, 1, 8);
+            __syncwarp();
+            // pass 3: covariance, lower triangle
+            for (int i = sub; i < m; i += 8) {
+                const unsigned rc = sring[i];
+                const float wt = __fdiv_rn(sval[i], wsum);
+                const float c0_ = __fsub_rn((float)(rc >> 16), a0), c1_ = __fsub_rn((float)(rc & 0xFFFFu), a1);
+                sstage[i] = __fmul_rn(__fmul_rn(c0_, wt), c0_);
+                sstage[kFitSmallMax + i] = __fmul_rn(__fmul_rn(c1_, wt), c0_);
+                sstage[2 * kFitSmallMax + i] = __fmul_rn(__fmul_rn(c1_, wt), c1_);
+            }
+            __syncwarp();
+            acc = (sub < 3 && m > 0) ? row_sum(sub, m) : 0.f;
+            float cov[4];
+            cov[0] = __shfl_sync(0xffffffffu, acc, 0, 8); cov[2] = __shfl_sync(0xffffffffu, acc, 1, 8); cov[3] = __shfl_sync(0xffffffffu, acc, 2, 8);
+            cov[1] = cov[2];
+            __syncwarp();
+            float eval[2], evec[4];
+            sym_eig<2>(cov, eval, evec);
+            const float d0 = evec[2], d1 = evec[3], n0 = evec[0], n1 = evec[1];
+            // pass 4: projection range (order-free) and mean |normal residual| (ordered)
+            float tmin = INFINITY, tmax = -INFINITY;
+            for (int i = sub; i < m; i += 8) {
+                const unsigned rc = sring[i];
+                const float c0_ = __fsub_rn((float)(rc >> 16), a0), c1_ = __fsub_rn((float)(rc & 0xFFFFu), a1);
+                const float tt = __fadd_rn(__fmul_rn(c0_, d0), __fmul_rn(c1_, d1));
+                tmin = fminf(tmin, tt); tmax = fmaxf(tmax, tt);
+                sstage[i] = fabsf(__fadd_rn(__fmul_rn(c0_, n0), __fmul_rn(c1_, n1)));
+            }
+            __syncwarp();
+            acc = (sub == 0 && m > 0) ? row_sum(0, m) : 0.f;
+#pragma unroll
+            for (int sft = 4; sft > 0; sft >>= 1) {
+                tmin = fminf(tmin, __shfl_xor_sync(0xffffffffu, tmin, sft));
+                tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, sft));
+            }
+            if (on && sub == 0) {
+                SegRec sg;
+                sg.y1 = __fadd_rn(a0, __fmul_rn(d0, tmin)); sg.x1 = __fadd_rn(a1, __fmul_rn(d1, tmin));
+                sg.y2 = __fadd_rn(a0, __fmul_rn(d0, tmax)); sg.x2 = __fadd_rn(a1, __fmul_rn(d1, tmax));
+                sg.weight = __fdiv_rn(wsum, (float)m);
+                sg.err = __fdiv_rn(acc, (float)m);
+                sg.group_id = -1;
+                reinterpret_cast<SegRec *>(K.seg)[ko + comp] = sg;
+            }
+            __syncwarp();
+        }
+    }
 }
 
 // debug/test helper: label plane (kept component index, -1 elsewhere) from the pixel lists
@@ -298,6 +444,10 @@ __global__ void k_labels(Planes P, Comps K, FrameCtrl * ctrl, int * labels, int 
 void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * ctrl, int n_slots, int rounds_total, cudaStream_t st)
 {
     LRB_CARVEOUT(k_comp_select); LRB_CARVEOUT(k_fit_segments);
+    // 14 KB of shared memory per CTA: without a stated preference the driver would give the SM its largest shared-memory split to
+    // fit sixteen CTAs, and the kernels of the other engines on that SM would be left with a 28 KB L1
+    static PerDeviceOnce once;
+    once.run([&] { cudaFuncSetAttribute(k_fit_segments, cudaFuncAttributePreferredSharedMemoryCarveout, 50); });
     k_comp_select<<<n_slots, 1024, 0, st>>>(S, K, ctrl, rounds_total);
     dim3 grid(max(1, 148 * 8 / max(1, min(n_slots, 8))), n_slots);
     k_fit_segments<<<grid, FIT_WARPS * 32, 0, st>>>(P, S, K, ctrl);
