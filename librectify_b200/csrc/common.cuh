@@ -60,7 +60,8 @@ __device__ __forceinline__ float orient_energy(float dx, float dy, int b)
 
 // ---- seed ordering ------------------------------------------------------------------------------------------------
 constexpr int kSeedBuckets = 4096;
-constexpr int kSampWorkers = 128, kSampRecords = 512;
+constexpr int kSampWorkers = 128, kSampRecords = 512;          // speculative sampler: workers x records per worker (throughput shape)
+constexpr int kSampWorkersMax = 512;                          // latency shape (one or two frames): 512 workers x 128 records, same memory
 constexpr int kFloodWindowMin = 4096, kFloodWindowDiv = 6;   // steady window: max(4096, n_seeds / 6) seeds per round ...
 constexpr int kFloodWindowFirst = 256;                       // ... reached by doubling from this size in round 0
 constexpr int kFitSmallMax = 32;                             // components up to this size are fitted by eight lanes (k5_fit.cu)
@@ -175,7 +176,8 @@ struct Lines {                  // per slot: filtered segments and the pencil mo
     int * tmp;                  // inlier list of the winning hypothesis
     int * pairs;                // 2 x T per slot: sampled positions in the observation list
     float * scores;             // kMaxModels x T per slot (-1 = rejected by sample_check); kept for the parity tests
-    // speculative sampler workers (k7_sampler.cu): kSampWorkers x kSampRecords records per slot
+    // speculative sampler workers (k7_sampler.cu): samp_workers x samp_records records per slot (their product is fixed)
+    int samp_workers, samp_records;
     unsigned * rec_start;       // sample start, relative to the solve's first stream position
     int * rec_pair;             // 2 per record: the two picks
     int * rec_cnt1; int * rec_cnt;   // records made inside the own segment / in total

@@ -216,7 +216,8 @@ int ensure_workspace(lrb_engine * e, int w, int h)
         e->L.inlier = carve<int>(p, (size_t)cap_lines * G); e->L.garbage = carve<int>(p, (size_t)cap_lines * G);
         e->L.obs = carve<int>(p, (size_t)cap_lines * G); e->L.tmp = carve<int>(p, (size_t)cap_lines * G);
         e->L.pairs = carve<int>(p, (size_t)2 * kT * G); e->L.scores = carve<float>(p, (size_t)kMaxModels * kT * G);
-        const size_t nw = (size_t)kSampWorkers * G, nr = nw * kSampRecords;
+        const size_t nw = (size_t)kSampWorkersMax * G, nr = (size_t)kSampWorkers * kSampRecords * G;
+        e->L.samp_workers = kSampWorkers; e->L.samp_records = kSampRecords;
         e->L.rec_start = carve<unsigned>(p, nr); e->L.rec_pair = carve<int>(p, 2 * nr);
         e->L.rec_cnt1 = carve<int>(p, nw); e->L.rec_cnt = carve<int>(p, nw); e->L.rec_next = carve<unsigned>(p, nw);
         e->L.rec_link = carve<int>(p, 2 * nw);
@@ -265,6 +266,15 @@ struct Tick {
     void end() { if (e->prof) cudaEventRecord(e->ev[LRB_T_COUNT], e->st); }
 };
 
+// The sampler's shape: a large group wants few workers (less speculative overlap), one or two frames are latency-bound and want
+// short chains — four times the workers with a quarter of the records each (same memory, same result).
+Lines lines_view(const lrb_engine * e, int n)
+{
+    Lines L = e->L;
+    if (n <= 2) { L.samp_workers = kSampWorkersMax; L.samp_records = kSampWorkers * kSampRecords / kSampWorkersMax; }
+    return L;
+}
+
 void enqueue_tail(lrb_engine * e, int n, float min_length, int rounds_total, Tick & tk)
 {
     tk.at(LRB_T_FIT);
@@ -273,7 +283,7 @@ void enqueue_tail(lrb_engine * e, int n, float min_length, int rounds_total, Tic
     if (e->refine) e->kernels += launch_refine(e->K, e->ctrl, n, e->st);
     launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds_total, e->refine, e->st);
     tk.at(LRB_T_RANSAC);
-    launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st, e->prof ? e->ev_score : nullptr);
+    launch_ransac(lines_view(e, n), e->ctrl, n, e->stream, e->stream_len, kT, e->st, e->prof ? e->ev_score : nullptr);
     e->kernels += 2 + 1 + 6 * kMaxModels + 1;
 }
 
@@ -437,14 +447,14 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     stage(LRB_T_SEEDS);
     launch_seed_order(e->P, Sg, e->ctrl, n, e->S.cap, e->st);
     stage(LRB_T_FLOOD);
-    int rounds = (n <= 2) ? 16 : kInitialRounds;
+    int rounds = (n <= 2) ? 12 : kInitialRounds;       // one or two frames at the steady window need 9-10 rounds; every blind empty round is four launches of latency
     e->kernels += launch_flood_rounds(e->P, Sg, e->K, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
     e->kernels += 2 + 1 + 3;
     if (debug_sync) {
         stage(LRB_T_FIT); launch_fit(e->P, e->S, e->K, e->ctrl, n, rounds, e->st);
         stage(LRB_T_MODEL); if (e->refine) e->kernels += launch_refine(e->K, e->ctrl, n, e->st);
         launch_filter_model(e->K, e->L, e->ctrl, n, min_length, rounds, e->refine, e->st);
-        stage(LRB_T_RANSAC); launch_ransac(e->L, e->ctrl, n, e->stream, e->stream_len, kT, e->st, e->prof ? e->ev_score : nullptr);
+        stage(LRB_T_RANSAC); launch_ransac(lines_view(e, n), e->ctrl, n, e->stream, e->stream_len, kT, e->st, e->prof ? e->ev_score : nullptr);
         stage(LRB_T_READBACK);
         order.resize(order.size() - 4);
         if (stage_err != cudaSuccess) return fail(-2, "debug sync: a stage failed (see stderr): %s", cudaGetErrorString(stage_err));

@@ -32,6 +32,7 @@ namespace {
 
 constexpr int FL_WARPS = 4;
 constexpr int kPoolGranule = 256;  // list space a warp takes from the pool at a time (words)
+constexpr int kVerifyWide = 64;   // regions longer than this are verified by a whole warp instead of eight lanes
 constexpr int FT_SMALL = 16;      // tiles a flood may touch before it moves from shared memory to a global-memory table
 
 // reference src/filter.cpp:113-116 neighbour order (dr, dc) — used by the serial fallback below
@@ -651,10 +652,12 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         const bool valid = rank < hi && S.status[so + rank] == kStatusLive;
         const unsigned key = (epoch << 24) | (unsigned)rank;
         const int size = valid ? S.size[so + rank] : 0;
-        const unsigned * list = pool + (valid ? S.list_head[so + rank] : 0);
+        const int lhead = valid ? S.list_head[so + rank] : 0;
+        const unsigned * list = pool + lhead;
+        const bool big = size > kVerifyWide;                      // a long region: the whole warp takes it afterwards
         // pass 1: is every pixel still stamped with this seed's key?
         bool mine = true;
-        for (int i = sub; i < size; i += 32) {
+        if (!big) for (int i = sub; i < size; i += 32) {
             unsigned w[4], o[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) w[u] = (i + 8 * u < size) ? __ldcg(list + i + 8 * u) : 0u;
@@ -664,14 +667,40 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
             for (int u = 0; u < 4; ++u) mine &= (o[u] == key);
         }
         const unsigned bm = __ballot_sync(0xffffffffu, mine);
-        if (!valid) continue;
-        if (((bm >> (8 * grp)) & 0xFFu) != 0xFFu) { ++live; first = min(first, rank); continue; }
-        // pass 2: the region is final — it becomes part of the visited mask (whether or not it is kept later)
-        for (int i = sub; i < size; i += 8) {
-            const unsigned w = __ldcg(list + i);
-            vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
+        unsigned bigm = __ballot_sync(0xffffffffu, big && sub == 0);
+        if (valid && !big) {
+            if (((bm >> (8 * grp)) & 0xFFu) != 0xFFu) { ++live; first = min(first, rank); }
+            else {
+                // pass 2: the region is final — it becomes part of the visited mask (whether or not it is kept later)
+                for (int i = sub; i < size; i += 8) {
+                    const unsigned w = __ldcg(list + i);
+                    vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
+                }
+                if (sub == 0) S.status[so + rank] = key;
+            }
         }
-        if (sub == 0) S.status[so + rank] = key;
+        while (bigm) {                                            // long regions, one after the other, 32 lanes x 4 entries in flight
+            const int src = __ffs(bigm) - 1; bigm &= bigm - 1;
+            const int brank = __shfl_sync(0xffffffffu, rank, src), bsize = __shfl_sync(0xffffffffu, size, src);
+            const unsigned * bl = pool + __shfl_sync(0xffffffffu, lhead, src);
+            const unsigned bkey = (epoch << 24) | (unsigned)brank;
+            bool m2 = true;
+            for (int i = lane; i < bsize && m2; i += 128) {
+                unsigned w[4], o[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) w[u] = (i + 32 * u < bsize) ? __ldcg(bl + i + 32 * u) : 0u;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) o[u] = (i + 32 * u < bsize) ? __ldcg(owner + (size_t)(w[u] >> 16) * P.pitch + (w[u] & 0xFFFFu)) : bkey;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) m2 &= (o[u] == bkey);
+            }
+            if (!__all_sync(0xffffffffu, m2)) { if (lane == src) { ++live; first = min(first, brank); } continue; }
+            for (int i = lane; i < bsize; i += 32) {
+                const unsigned w = __ldcg(bl + i);
+                vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
+            }
+            if (lane == src) S.status[so + brank] = bkey;
+        }
     }
     if (sub != 0) live = 0;
     if (live) { atomicAdd(&C.win_live, live); atomicMin(&C.win_first, first); }
@@ -800,10 +829,10 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
         dim3 gp(max(1, min((seeds_hint + 255) / 256, 64)), ns);
         LRB_CARVEOUT(kern); LRB_CARVEOUT(k_flood_verify); LRB_CARVEOUT(k_flood_prune);
         // the sub-warp passes take four / two seeds per warp
-        const int sblocks = max(1, min((seeds_hint + 4 * FL_WARPS - 1) / (4 * FL_WARPS), (n_sm * 6 + ns - 1) / ns));
+        const int sblocks = max(1, min((seeds_hint + 4 * FL_WARPS - 1) / (4 * FL_WARPS), (n_sm * 8 + ns - 1) / ns));
         const int mblocks = max(1, min((seeds_hint + 2 * FL_WARPS - 1) / (2 * FL_WARPS), (n_sm * 6 + ns - 1) / ns / 2));
         dim3 gs(sblocks, ns), gm(mblocks, ns);
-        LRB_CARVEOUT((k_flood_small<8, 6>)); LRB_CARVEOUT((k_flood_small<16, 6>));
+        LRB_CARVEOUT((k_flood_small<8, 8>)); LRB_CARVEOUT((k_flood_small<16, 6>));
         static const int small_mode = [] { const char * v = getenv("LRB_FLOOD_SMALL_MODE"); return v ? atoi(v) : 0; }();
         for (int r = round_begin; r < round_end; ++r) {
             if (prune && r > 0) { k_flood_prune<<<gp, 256, 0, st>>>(P, S, ctrl, r, s0); ++launches; }
@@ -813,7 +842,7 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
             // what the 8-lane pass escalates (those floods are long lines, not slightly larger blobs) and costs 7 % of the job
             // throughput (profiles/r2_flood_regions.md), so it is off by default
             static const bool mid = [] { const char * v = getenv("LRB_FLOOD_MID"); return v && atoi(v) != 0; }();
-            k_flood_small<8, 6><<<gs, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode, mid ? 0 : 1);
+            k_flood_small<8, 8><<<gs, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode, mid ? 0 : 1);
             LRB_TRACE_SYNC("sub-warp pass (8 lanes)");
             if (mid) {
                 k_flood_small<16, 6><<<gm, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode, 1);

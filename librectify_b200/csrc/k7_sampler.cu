@@ -79,7 +79,7 @@ __device__ __forceinline__ bool chain_walk(const unsigned * __restrict__ stream,
 
 struct SamplerPlan { unsigned long long o0; unsigned long long L; long long n; };
 
-__device__ __forceinline__ SamplerPlan make_plan(const FrameCtrl & C, int solve, int T)
+__device__ __forceinline__ SamplerPlan make_plan(const FrameCtrl & C, int solve, int T, int workers)
 {
     SamplerPlan pl;
     pl.n = C.n_obs[solve];
@@ -87,7 +87,7 @@ __device__ __forceinline__ SamplerPlan make_plan(const FrameCtrl & C, int solve,
     // expected draws of the whole solve: T * 2(n+1)/3 (the second pick of a 2-subset of [0,n) is at 2(n+1)/3 - 1 on
     // average); relative spread over 10^4 samples ~0.4 %, so +3 % covers it — the last worker has no upper bound anyway
     const unsigned long long D = (2ull * (unsigned long long)(pl.n + 1) * (unsigned long long)T) / 3ull;
-    pl.L = (D + D / 32) / kSampWorkers + 1;
+    pl.L = (D + D / 32) / workers + 1;
     return pl;
 }
 
@@ -99,10 +99,10 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_segments(Lines L, FrameCtrl 
     FrameCtrl & C = ctrl[slot];
     if (C.n_solves != solve || C.num_obs < 2) return;
     const int j = blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (j >= kSampWorkers) return;
+    if (j >= L.samp_workers) return;
     const int lane = threadIdx.x & 31;
-    const SamplerPlan pl = make_plan(C, solve, T);
-    const size_t ro = ((size_t)slot * kSampWorkers + j) * kSampRecords;
+    const SamplerPlan pl = make_plan(C, solve, T, L.samp_workers);
+    const size_t ro = ((size_t)slot * L.samp_workers + j) * L.samp_records;
     unsigned * rs = L.rec_start + ro; int2 * rp = reinterpret_cast<int2 *>(L.rec_pair) + ro;
     const unsigned long long sj = pl.o0 + (unsigned long long)j * pl.L;
     const unsigned long long send = sj + pl.L;      // the planned range already carries a 3 % (> 7 sigma) margin; beyond it the tail walk takes over
@@ -111,10 +111,10 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_segments(Lines L, FrameCtrl 
     const bool ok = chain_walk(stream, stream_len, pl.n, sj, [&](unsigned long long start, int s0, int s1, unsigned long long nx) {
         if (lane == 0) { rs[cnt] = (unsigned)(start - pl.o0); rp[cnt] = make_int2(s0, s1); }
         ++cnt; next = nx;
-        return (nx < send) && (cnt < kSampRecords - 1);
+        return (nx < send) && (cnt < L.samp_records - 1);
     });
     if (lane == 0) {
-        const size_t wo = (size_t)slot * kSampWorkers + j;
+        const size_t wo = (size_t)slot * L.samp_workers + j;
         L.rec_cnt1[wo] = cnt; L.rec_cnt[wo] = cnt; L.rec_next[wo] = (unsigned)(next - pl.o0);
         L.rec_link[2 * wo] = -1; L.rec_link[2 * wo + 1] = 0;
         if (!ok && j == 0) C.stream_overflow = 1;      // only the true chain's own stretch must exist; speculative workers may fall off the end
@@ -130,23 +130,23 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_link(Lines L, FrameCtrl * ct
     FrameCtrl & C = ctrl[slot];
     if (C.n_solves != solve || C.num_obs < 2) return;
     const int j = blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (j >= kSampWorkers - 1) return;                 // the last worker has no successor
+    if (j >= L.samp_workers - 1) return;                 // the last worker has no successor
     const int lane = threadIdx.x & 31;
-    const SamplerPlan pl = make_plan(C, solve, T);
-    const size_t wo = (size_t)slot * kSampWorkers + j;
+    const SamplerPlan pl = make_plan(C, solve, T, L.samp_workers);
+    const size_t wo = (size_t)slot * L.samp_workers + j;
     if (L.rec_cnt1[wo] < 0) return;                    // ran out of stream in phase 1
-    const size_t ro = wo * kSampRecords;
+    const size_t ro = wo * L.samp_records;
     unsigned * rs = L.rec_start + ro; int2 * rp = reinterpret_cast<int2 *>(L.rec_pair) + ro;
     int cnt = L.rec_cnt[wo];
-    if (cnt >= kSampRecords - 1) return;               // record space used up inside its own segment: no link
+    if (cnt >= L.samp_records - 1) return;               // record space used up inside its own segment: no link
 
     // is `start` (relative to o0) a recorded phase-1 sample start of the segment that contains it?
     auto lookup = [&](unsigned rel, int & k_out) -> int {
-        int k = (int)min((unsigned long long)rel / pl.L, (unsigned long long)(kSampWorkers - 1));
+        int k = (int)min((unsigned long long)rel / pl.L, (unsigned long long)(L.samp_workers - 1));
         k_out = k;
-        const size_t wk = (size_t)slot * kSampWorkers + k;
+        const size_t wk = (size_t)slot * L.samp_workers + k;
         int c1 = L.rec_cnt1[wk]; if (c1 < 0) c1 = -1 - c1;
-        const unsigned * rk = L.rec_start + wk * kSampRecords;
+        const unsigned * rk = L.rec_start + wk * L.samp_records;
         int found = -1;
         for (int i0 = 0; i0 < c1; i0 += 32) {
             const int i = i0 + lane;
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_link(Lines L, FrameCtrl * ct
             ++cnt; next = nx;
             int k; const int b = lookup((unsigned)(nx - pl.o0), k);
             if (b >= 0 && k != j) { lk = k; lb = b; return false; }
-            return cnt < kSampRecords - 1;
+            return cnt < L.samp_records - 1;
         });
     }
     if (lane == 0) {
@@ -177,15 +177,15 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_link(Lines L, FrameCtrl * ct
 // ---- phase 3: follow the links from worker 0 and emit the first T samples in chain order -----------------------------------
 __global__ void __launch_bounds__(1024) k_sampler_stitch(Lines L, FrameCtrl * ctrl, int solve, int T)
 {
-    __shared__ int s_w[kSampWorkers], s_b[kSampWorkers], s_c[kSampWorkers], s_off[kSampWorkers];
+    __shared__ int s_w[kSampWorkersMax], s_b[kSampWorkersMax], s_c[kSampWorkersMax], s_off[kSampWorkersMax];
     __shared__ int s_n, s_total;
     const int slot = blockIdx.x;
     FrameCtrl & C = ctrl[slot];
     if (C.n_solves != solve || C.num_obs < 2) return;
-    const size_t w0 = (size_t)slot * kSampWorkers;
-    __shared__ int t_cnt[kSampWorkers], t_lk[kSampWorkers], t_lb[kSampWorkers];
-    __shared__ unsigned t_next[kSampWorkers];
-    for (int i = threadIdx.x; i < kSampWorkers; i += blockDim.x) {
+    const size_t w0 = (size_t)slot * L.samp_workers;
+    __shared__ int t_cnt[kSampWorkersMax], t_lk[kSampWorkersMax], t_lb[kSampWorkersMax];
+    __shared__ unsigned t_next[kSampWorkersMax];
+    for (int i = threadIdx.x; i < L.samp_workers; i += blockDim.x) {
         t_cnt[i] = L.rec_cnt[w0 + i]; t_lk[i] = L.rec_link[2 * (w0 + i)]; t_lb[i] = L.rec_link[2 * (w0 + i) + 1]; t_next[i] = L.rec_next[w0 + i];
     }
     __syncthreads();
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(1024) k_sampler_stitch(Lines L, FrameCtrl * ct
         int cur = 0, b = 0, off = 0, nseg = 0;
         unsigned long long endpos = C.stream_pos;
         bool complete = false;
-        while (cur >= 0 && nseg < kSampWorkers) {
+        while (cur >= 0 && nseg < L.samp_workers) {
             const int have = t_cnt[cur] - b;                 // samples worker `cur` contributes from its entry point on
             const int take = min(have, T - off);
             s_w[nseg] = cur; s_b[nseg] = b; s_c[nseg] = take; s_off[nseg] = off; ++nseg;
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(1024) k_sampler_stitch(Lines L, FrameCtrl * ct
             if (off >= T) {
                 // start of sample T = start of the record after the last one taken, or the worker's saved continuation
                 const int last = b + take;                             // index of the first record NOT taken
-                const unsigned rel = (last < t_cnt[cur]) ? L.rec_start[(w0 + cur) * kSampRecords + last] : t_next[cur];
+                const unsigned rel = (last < t_cnt[cur]) ? L.rec_start[(w0 + cur) * L.samp_records + last] : t_next[cur];
                 endpos = C.stream_pos + rel; complete = true; break;
             }
             const int lk = t_lk[cur];
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(1024) k_sampler_stitch(Lines L, FrameCtrl * ct
     for (int j = threadIdx.x; j < total; j += blockDim.x) {
         int lo_ = 0, hi_ = nseg - 1;
         while (lo_ < hi_) { const int mid = (lo_ + hi_ + 1) >> 1; if (s_off[mid] <= j) lo_ = mid; else hi_ = mid - 1; }
-        pairs[j] = reinterpret_cast<const int2 *>(L.rec_pair)[(w0 + s_w[lo_]) * kSampRecords + s_b[lo_] + (j - s_off[lo_])];
+        pairs[j] = reinterpret_cast<const int2 *>(L.rec_pair)[(w0 + s_w[lo_]) * L.samp_records + s_b[lo_] + (j - s_off[lo_])];
     }
 }
 
@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(32) k_sampler_tail(Lines L, FrameCtrl * ctrl, 
 void launch_sampler(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
                     int solve, int T, cudaStream_t st)
 {
-    dim3 g((kSampWorkers + 3) / 4, n_slots);
+    dim3 g((L.samp_workers + 3) / 4, n_slots);
     LRB_CARVEOUT(k_sampler_segments); LRB_CARVEOUT(k_sampler_link); LRB_CARVEOUT(k_sampler_stitch); LRB_CARVEOUT(k_sampler_tail);
     k_sampler_segments<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
     k_sampler_link<<<g, 128, 0, st>>>(L, ctrl, stream, stream_len, solve, T);
