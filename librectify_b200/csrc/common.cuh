@@ -111,6 +111,9 @@ struct FrameCtrl {
     unsigned long long dbg_maxdur;   // (ns << 24) | px of the slowest flood
     unsigned long long dbg_sumdur;
     int dbg_slow[4];
+    unsigned long long dbg_rmax[24];  // per round: (ns << 24) | px of the slowest full-tile flood (LRB_FLOOD_STATS builds)
+    int dbg_rtiles[24];
+    long long dbg_replay[4];          // clock64 spans of the tie-order replay: phase 1, phase 2, fix-up (LRB_FLOOD_STATS builds)
 };
 
 // ---- views passed to kernels by value -----------------------------------------------------------------------------

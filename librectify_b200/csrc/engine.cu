@@ -508,6 +508,8 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         CK(cudaGetLastError());
     }
     if (getenv("LRB_DEBUG_STATS")) for (int i = 0; i < n; ++i) { const FrameCtrl & C = e->h_ctrl[i];
+        fprintf(stderr, "[lrb] slot %d replay: tied %d steps %d, cycles phase1 %lld phase2 %lld fixup %lld, small ranges %lld\n", i, C.n_tied, C.replay_steps, C.dbg_replay[0], C.dbg_replay[1], C.dbg_replay[2], C.dbg_replay[3]);
+        { fprintf(stderr, "[lrb] slot %d slowest full-tile flood per round (us/px/tiles, by epoch):", i); for (int r = 0; r < 24; ++r) if (C.dbg_rmax[r]) fprintf(stderr, " %d:%.0f/%d/%d", r, (C.dbg_rmax[r] >> 24) * 1e-3, (int)(C.dbg_rmax[r] & 0xFFFFFF), C.dbg_rtiles[r]); fprintf(stderr, "\n"); }
         fprintf(stderr, "[lrb] slot %d: seeds %d rounds %d floods %d big %d tiles %d px %d maxpx %d committed px %d comps %d slowest flood %.1f us (%d px; visits %d iters %d evals %d tiles %d) mean %.2f us\n", i, C.n_seeds, C.rounds_run, C.dbg_floods, C.dbg_big, C.dbg_tiles, C.dbg_px, C.dbg_maxpx, C.dbg_commit_px, C.n_comp, (C.dbg_maxdur >> 24) * 1e-3, (int)(C.dbg_maxdur & 0xFFFFFF), C.dbg_slow[0], C.dbg_slow[1], C.dbg_slow[2], C.dbg_slow[3], C.dbg_sumdur * 1e-3 / std::max(1, C.dbg_floods)); }
     e->prof = prof_saved;
     e->next_epoch = epoch_first - (unsigned)rounds - 2;

@@ -89,7 +89,8 @@ __device__ __forceinline__ int rp_median3(const uint2 * a, int f, int l)
 
 // One __unguarded_partition_pivot of [f, l) by one warp on a range in shared memory (phase 2).  Lp / Rp: 16-bit scratch of the
 // range.  Returns the cut; tied_left = tied elements in [f, cut) afterwards.
-__device__ int rp_partition_small(uint2 * a, unsigned short * Lp, unsigned short * Rp, int f, int l, int tied_total, int & tied_left)
+template <class IdxT>
+__device__ int rp_partition_small(uint2 * a, IdxT * Lp, IdxT * Rp, int f, int l, int tied_total, int & tied_left)
 {
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -98,36 +99,58 @@ __device__ int rp_partition_small(uint2 * a, unsigned short * Lp, unsigned short
     if (lane == 0) { const uint2 t = a[f]; a[f] = a[m]; a[m] = t; }
     __syncwarp();
     const unsigned pv = a[f].x;
+    // U chunks of 32 keys in flight per memory round trip (the range may live in global memory: phase 2a)
+    constexpr int U = sizeof(IdxT) == 4 ? 4 : 2;
     int cL = 0;                                                            // left stoppers, in scan order: !(x before pivot)
-    for (int base = f + 1; base < l; base += 32) {
-        const int i = base + lane;
-        const bool fl = i < l && !rp_before(a[i].x, pv);
-        const unsigned bal = __ballot_sync(0xffffffffu, fl);
-        if (fl) Lp[cL + __popc(bal & lt)] = (unsigned short)i;
-        cL += __popc(bal);
+    for (int base = f + 1; base < l; base += 32 * U) {
+        unsigned kk[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { const int i = base + 32 * u + lane; kk[u] = i < l ? a[i].x : 0u; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + 32 * u + lane;
+            const bool fl = i < l && !rp_before(kk[u], pv);
+            const unsigned bal = __ballot_sync(0xffffffffu, fl);
+            if (fl) Lp[cL + __popc(bal & lt)] = (IdxT)i;
+            cL += __popc(bal);
+        }
     }
     int cR = 0;                                                            // right stoppers, from the right: !(pivot before x)
-    for (int base = l - 1; base > f; base -= 32) {
-        const int i = base - lane;
-        const bool fl = i > f && !rp_before(pv, a[i].x);
-        const unsigned bal = __ballot_sync(0xffffffffu, fl);
-        if (fl) Rp[cR + __popc(bal & lt)] = (unsigned short)i;
-        cR += __popc(bal);
+    for (int base = l - 1; base > f; base -= 32 * U) {
+        unsigned kk[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { const int i = base - 32 * u - lane; kk[u] = i > f ? a[i].x : 0u; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base - 32 * u - lane;
+            const bool fl = i > f && !rp_before(pv, kk[u]);
+            const unsigned bal = __ballot_sync(0xffffffffu, fl);
+            if (fl) Rp[cR + __popc(bal & lt)] = (IdxT)i;
+            cR += __popc(bal);
+        }
     }
     __syncwarp();
     const int mn = min(cL, cR);
     int K = 0;
-    for (int kb0 = 0; kb0 < mn; kb0 += 32) {                               // the k-th left stopper <-> the k-th right stopper while left of it
-        const int k = kb0 + lane;
-        bool sw = false;
-        if (k < mn) {
-            const int lp = Lp[k], rp = Rp[k];
-            sw = lp < rp;
-            if (sw) { const uint2 x = a[lp], y = a[rp]; a[lp] = y; a[rp] = x; }
+    for (int kb0 = 0; kb0 < mn; kb0 += 32 * U) {                           // the k-th left stopper <-> the k-th right stopper while left of it
+        int lp[U], rp[U]; bool sw[U]; uint2 x[U], y[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int k = kb0 + 32 * u + lane;
+            lp[u] = k < mn ? (int)Lp[k] : 1; rp[u] = k < mn ? (int)Rp[k] : 0;
+            sw[u] = k < mn && lp[u] < rp[u];
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, sw);
-        K += __popc(bal);
-        if (bal != 0xffffffffu) break;
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (sw[u]) { x[u] = a[lp[u]]; y[u] = a[rp[u]]; }
+        bool done = false;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (sw[u]) { a[lp[u]] = y[u]; a[rp[u]] = x[u]; }              // exchanges are a prefix in k: what follows a non-exchange stays put
+            const unsigned bal = __ballot_sync(0xffffffffu, sw[u]);
+            K += __popc(bal);
+            done |= bal != 0xffffffffu;
+        }
+        if (done) break;
     }
     __syncwarp();
     const int cut = (K == 0) ? (int)Lp[0] : min(K < cL ? (int)Lp[K] : INT_MAX, (int)Rp[K - 1]);
@@ -142,6 +165,7 @@ __device__ int rp_partition_small(uint2 * a, unsigned short * Lp, unsigned short
 }
 
 constexpr int kSmall = 512;                   // ranges up to this size are finished by one warp in shared memory
+constexpr int kMid = 2048;                    // ranges up to this size leave the level-synchronous phase: one warp follows each of them in global memory
 constexpr int kMaxSeg = 64;                   // ranges of one level processed together in phase 1
 constexpr int kWorkers = 8;                   // warps that take part in phase 2
 constexpr int kStack = 48;                    // >= 2 * log2(kSmall) + slack: pending right parts below one small range
@@ -184,10 +208,13 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
         int lg = 0; while ((2 << lg) <= n) ++lg;                           // std::__lg(n)
         const int4 root = make_int4(0, n, depth_override >= 0 ? depth_override : 2 * lg, n_tied);
         n_cur = 0; n_next = 0; n_small = 0; small_head = 0; steps = 0;
-        if (n > kSmall) { qa[0] = root; n_cur = 1; } else { qs[0] = root; n_small = 1; }
+        if (n > kMid) { qa[0] = root; n_cur = 1; } else { qs[0] = root; n_small = 1; }
     }
     __syncthreads();
 
+#ifdef LRB_FLOOD_STATS
+    const long long t_p0 = clock64();
+#endif
     // ---- phase 1: ranges longer than kSmall, level by level ---------------------------------------------------------------
     RpPhase1 & A = sh.p1;
     while (true) {
@@ -323,7 +350,7 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
                     for (int c = 0; c < 2; ++c) {
                         const int len = kid[c].y - kid[c].x;
                         if (len <= kSortThreshold || kid[c].w < 2) continue;
-                        if (len > kSmall) qb[atomicAdd(&n_next, 1)] = kid[c];
+                        if (len > kMid) qb[atomicAdd(&n_next, 1)] = kid[c];
                         else qs[atomicAdd(&n_small, 1)] = kid[c];
                     }
                     atomicAdd(&steps, 1);
@@ -337,6 +364,51 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
     }
     __syncthreads();
 
+#ifdef LRB_FLOOD_STATS
+    const long long t_p1 = clock64();
+#endif
+    // ---- phase 2a: ranges of kSmall+1 .. kMid elements, one warp each, in place in global memory (all 32 warps) ------------
+    // The level-synchronous phase pays its barriers and memory round trips once per RANGE of a level (the CTA walks the ranges
+    // one after the other), which is right for a few long ranges and wrong for the dozens of mid-sized ones a frame with 40 tied
+    // pairs produces two or three levels down (measured: 300 of the kernel's 400 us).  Here every warp follows one such range
+    // down on its own stack; what falls to kSmall elements or below joins the list of small ranges.
+    {
+        __shared__ int mid_head;
+        if (tid == 0) mid_head = 0;
+        __syncthreads();
+        const int n_mid = n_small;                                        // items listed by phase 1 (any size up to kMid)
+        __syncthreads();
+        int4 stack[kStack];
+        int my_steps = 0;
+        while (true) {
+            int item = 0;
+            if (lane == 0) item = atomicAdd(&mid_head, 1);
+            item = __shfl_sync(0xffffffffu, item, 0);
+            if (item >= n_mid) break;
+            const int4 g = qs[item];
+            if (g.y - g.x <= kSmall) continue;                            // phase 2 takes it
+            int sp = 0;
+            stack[sp++] = g;
+            while (sp > 0) {
+                const int4 r = stack[--sp];
+                int f = r.x, l = r.y, d = r.z, t = r.w;
+                while (l - f > kSortThreshold && t >= 2) {
+                    if (l - f <= kSmall) { if (lane == 0) qs[atomicAdd(&n_small, 1)] = make_int4(f, l, d, t); break; }
+                    if (d == 0) { if (lane == 0) rp_heap_sort(a + f, l - f); __syncwarp(); break; }
+                    --d;
+                    int tl;
+                    const int cut = rp_partition_small<int>(a, Lp + f + 1, Rp + f + 1, f, l, t, tl);
+                    ++my_steps;
+                    if (l - cut > kSortThreshold && t - tl >= 2 && sp < kStack) stack[sp++] = make_int4(cut, l, d, t - tl);
+                    l = cut; t = tl;
+                }
+            }
+            __syncwarp();
+        }
+        if (lane == 0 && my_steps) atomicAdd(&steps, my_steps);
+        __threadfence_block();
+        __syncthreads();
+    }
     // ---- phase 2: small ranges, one warp each, in shared memory ----------------------------------------------------------
     if (warp < kWorkers) {
         RpPhase2 & B = sh.p2;
@@ -351,6 +423,7 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
             if (item >= nsm) break;
             const int4 g = qs[item];
             const int len = g.y - g.x;
+            if (len > kSmall) continue;                                    // followed in phase 2a
             for (int i = lane; i < len; i += 32) sa[i] = a[g.x + i];
             __syncwarp();
             int sp = 0;
@@ -366,7 +439,7 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
                     }
                     --d;
                     int tl;
-                    const int cut = rp_partition_small(sa, sL, sR, f, l, t, tl);
+                    const int cut = rp_partition_small<unsigned short>(sa, sL, sR, f, l, t, tl);
                     ++my_steps;
                     if (l - cut > kSortThreshold && t - tl >= 2 && sp < kStack) stack[sp++] = make_int4(cut, l, d, t - tl);   // __introsort_loop(cut, last, depth_limit)
                     l = cut; t = tl;                                       // last = cut
@@ -380,6 +453,9 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
     }
     __syncthreads();
     if (tid == 0) C.replay_steps = steps;
+#ifdef LRB_FLOOD_STATS
+    const long long t_p2 = clock64();
+#endif
     if (!fixup) return;
     // ---- final order: stable by key of the arrangement above.  Only tied peaks move, inside their group's rank range. ----
     // (1) position of every rank
@@ -424,6 +500,10 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
         S.bin[so + fr] = (uint8_t)b;
         S.thr[so + fr] = __fmul_rn(kTraceKeep, orient_energy(P.dx[po], P.dy[po], b));      // reference src/filter.cpp:119-121
     }
+#ifdef LRB_FLOOD_STATS
+    __syncthreads();
+    if (tid == 0) { C.dbg_replay[0] = t_p1 - t_p0; C.dbg_replay[1] = t_p2 - t_p1; C.dbg_replay[2] = clock64() - t_p2; C.dbg_replay[3] = n_small; }
+#endif
 }
 
 } // namespace

@@ -376,6 +376,7 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
 #ifdef LRB_FLOOD_STATS
         { unsigned long long t_end; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end)); const unsigned long long d = t_end - t_begin;
           const unsigned long long pk = (d << 24) | (unsigned long long)(max(size, 0) & 0xFFFFFF);
+          { const int rr = (int)((0xFEu - epoch) % 24u); if (atomicMax(&C.dbg_rmax[rr], pk) < pk) C.dbg_rtiles[rr] = n_ent; }
           if (atomicMax(&C.dbg_maxdur, pk) < pk) { C.dbg_slow[0] = dbg[0]; C.dbg_slow[1] = dbg[1]; C.dbg_slow[2] = dbg[2]; C.dbg_slow[3] = n_ent; }
           atomicAdd(&C.dbg_sumdur, d); }
         atomicAdd(&C.dbg_floods, 1); atomicAdd(&C.dbg_tiles, n_ent); atomicAdd(&C.dbg_px, max(size, 0)); atomicMax(&C.dbg_maxpx, size);

@@ -177,41 +177,38 @@ __global__ void __launch_bounds__(32 * 4) k_sampler_link(Lines L, FrameCtrl * ct
 // ---- phase 3: follow the links from worker 0 and emit the first T samples in chain order -----------------------------------
 __global__ void __launch_bounds__(1024) k_sampler_stitch(Lines L, FrameCtrl * ctrl, int solve, int T)
 {
-    __shared__ int s_w[kSampWorkersMax], s_b[kSampWorkersMax], s_c[kSampWorkersMax], s_off[kSampWorkersMax];
+    __shared__ int s_w[kSampWorkersMax], s_b[kSampWorkersMax], s_off[kSampWorkersMax];
     __shared__ int s_n, s_total;
     const int slot = blockIdx.x;
     FrameCtrl & C = ctrl[slot];
     if (C.n_solves != solve || C.num_obs < 2) return;
     const size_t w0 = (size_t)slot * L.samp_workers;
-    __shared__ int t_cnt[kSampWorkersMax], t_lk[kSampWorkersMax], t_lb[kSampWorkersMax];
-    __shared__ unsigned t_next[kSampWorkersMax];
-    for (int i = threadIdx.x; i < L.samp_workers; i += blockDim.x) {
-        t_cnt[i] = L.rec_cnt[w0 + i]; t_lk[i] = L.rec_link[2 * (w0 + i)]; t_lb[i] = L.rec_link[2 * (w0 + i) + 1]; t_next[i] = L.rec_next[w0 + i];
-    }
+    // one 16-byte record per worker: the serial walk below pays ONE dependent shared-memory load per chain segment
+    __shared__ int4 t_node[kSampWorkersMax];             // records made, link worker, link record, continuation
+    for (int i = threadIdx.x; i < L.samp_workers; i += blockDim.x)
+        t_node[i] = make_int4(L.rec_cnt[w0 + i], L.rec_link[2 * (w0 + i)], L.rec_link[2 * (w0 + i) + 1], (int)L.rec_next[w0 + i]);
     __syncthreads();
     if (threadIdx.x == 0) {
         int cur = 0, b = 0, off = 0, nseg = 0;
         unsigned long long endpos = C.stream_pos;
-        bool complete = false;
         while (cur >= 0 && nseg < L.samp_workers) {
-            const int have = t_cnt[cur] - b;                 // samples worker `cur` contributes from its entry point on
+            const int4 nd = t_node[cur];
+            const int have = nd.x - b;                       // samples worker `cur` contributes from its entry point on
             const int take = min(have, T - off);
-            s_w[nseg] = cur; s_b[nseg] = b; s_c[nseg] = take; s_off[nseg] = off; ++nseg;
+            s_w[nseg] = cur; s_b[nseg] = b; s_off[nseg] = off; ++nseg;
             off += take;
             if (off >= T) {
                 // start of sample T = start of the record after the last one taken, or the worker's saved continuation
                 const int last = b + take;                             // index of the first record NOT taken
-                const unsigned rel = (last < t_cnt[cur]) ? L.rec_start[(w0 + cur) * L.samp_records + last] : t_next[cur];
-                endpos = C.stream_pos + rel; complete = true; break;
+                const unsigned rel = (last < nd.x) ? L.rec_start[(w0 + cur) * L.samp_records + last] : (unsigned)nd.w;
+                endpos = C.stream_pos + rel; break;
             }
-            const int lk = t_lk[cur];
-            if (lk < 0) { endpos = C.stream_pos + t_next[cur]; break; }
-            b = t_lb[cur]; cur = lk;
+            if (nd.y < 0) { endpos = C.stream_pos + (unsigned)nd.w; break; }
+            b = nd.z; cur = nd.y;
         }
         s_n = nseg; s_total = off;
         C.samp_done = off;                                           // < T: the sequential walk below finishes the job
         C.stream_pos = endpos;
-        (void)complete;
     }
     __syncthreads();
     // every output sample finds its chain segment by bisection over the segment offsets (one pass, all loads independent: the
