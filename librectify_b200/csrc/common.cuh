@@ -64,6 +64,7 @@ constexpr int kSampWorkers = 128, kSampRecords = 512;          // speculative sa
 constexpr int kSampWorkersMax = 512;                          // latency shape (one or two frames): 512 workers x 128 records, same memory
 constexpr int kFloodWindowMin = 4096, kFloodWindowDiv = 6;   // steady window: max(4096, n_seeds / 6) seeds per round ...
 constexpr int kFloodWindowFirst = 256;                       // ... reached by doubling from this size in round 0
+constexpr int kFloodWindowLate = 7;                          // ... and doubling again from this round on: the weak tail of the list (late rounds end with the tail of one slow blob each)
 constexpr int kFitSmallMax = 32;                             // components up to this size are fitted by eight lanes (k5_fit.cu)
 
 // ---- per-frame control block (device memory, one per slot; zeroed by k_frame_init) -------------------------------
@@ -133,6 +134,7 @@ struct Planes {                 // one frame slot = one set of planes; slot s li
 struct Seeds {                  // per slot: s * cap
     int cap;
     int win_min, win_div, win_first;          // seeds flooded per round: win_first in round 0, doubling up to max(win_min, n_seeds / win_div)
+    int win_late;                             // ... and doubling again from this round on (the weak tail of the list)
     unsigned * us_mag; unsigned * us_idx;     // unsorted (emission order)
     unsigned * b_mag;  unsigned * b_idx;      // bucketed
     unsigned * idx;                           // sorted by (mag desc, raster idx asc): rank -> pixel

@@ -236,6 +236,8 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     if (const char * v = getenv("LRB_WINDOW_MIN")) e->S.win_min = std::max(1, atoi(v));
     if (const char * v = getenv("LRB_WINDOW_DIV")) e->S.win_div = std::max(1, atoi(v));
     e->S.win_first = kFloodWindowFirst;
+    e->S.win_late = kFloodWindowLate;
+    if (const char * v = getenv("LRB_WINDOW_LATE")) e->S.win_late = std::max(1, atoi(v));
     if (const char * v = getenv("LRB_WINDOW_FIRST")) e->S.win_first = std::max(1, atoi(v));
     e->S.rows = h; e->S.roww = w;
     e->S.cap = cap_seeds; e->K.cap = cap_comp; e->K.cap_px = (int)std::min<size_t>(cap_px, 0x7fffffff); e->K.cap_pool = (int)std::min<size_t>(cap_pool, 0x7fffffe0); e->L.cap = cap_lines;

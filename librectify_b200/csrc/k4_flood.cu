@@ -716,7 +716,11 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         // seeds flooded per round: small at first — the strongest seeds own the long lines, and every other seed on such a line
         // would flood the whole line again, only to lose against the line's strongest seed — then doubling up to the steady size
         const long long grown = (long long)S.win_first << min(round + 1, 16);
-        const int budget = (int)min((long long)max(S.win_min, n / S.win_div), grown);
+        long long steady = max(S.win_min, n / S.win_div);
+        // late rounds: the seeds left are weak, their regions rarely touch, and every round ends with the tail of its slowest blob:
+        // the window doubles again from round win_late on, so that the rest of the list takes two or three rounds instead of five
+        if (round + 1 >= S.win_late) steady <<= min(round + 2 - S.win_late, 8);
+        const int budget = (int)min(steady, grown);
         const int nlo = failed ? min(firstf, hi) : hi;
         const int nhi = min(n, hi + max(0, budget - failed));
         C.win_lo = nlo; C.win_hi = nhi;

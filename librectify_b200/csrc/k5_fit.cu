@@ -21,6 +21,7 @@ namespace {
 
 constexpr int FIT_WARPS = 4;
 constexpr int FIT_RING = 256;        // power of two
+constexpr int FIT_CT = 8;            // owner-plane tiles cached per warp during the walk of a large component
 
 static __device__ __constant__ const int kDr[8] = {0, 0, 1, -1, -1, -1, 1, 1};
 static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
@@ -118,6 +119,8 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
     __shared__ __align__(16) float stage_all[FIT_WARPS][4 * 3 * kFitSmallMax];
     __shared__ float val_all[FIT_WARPS][FIT_RING];         // weights of a component that fits the ring (no re-reads from global memory)
     __shared__ unsigned ring_all[FIT_WARPS][FIT_RING];     // the last FIT_RING accepted pixels of the walk (the BFS frontier lives here)
+    __shared__ unsigned ctile_all[FIT_WARPS][FIT_CT * 32]; // per warp: 'pixel of this component, not listed yet' bitmaps of the last FIT_CT tiles touched
+    __shared__ int cid_all[FIT_WARPS][FIT_CT];
     static_assert(4 * kFitSmallMax <= FIT_RING && 4 * 3 * kFitSmallMax >= 3 * 32, "shared-memory sets of the two paths");
     const int slot = blockIdx.y;
     FrameCtrl & C = ctrl[slot];
@@ -128,6 +131,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
     unsigned * ring = ring_all[warp];
     float * vring = val_all[warp];
     const int * biglist = S.esc + (size_t)slot * S.cap;
+    unsigned * ctile = ctile_all[warp]; int * cid = cid_all[warp];
     const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap, pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
     const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
@@ -153,7 +157,8 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
         // ---- pixel list in the reference's acceptance order (filter.cpp:123-151) ----------------------------------
         // The frontier is read from a shared-memory ring (one memory round trip per step: the owner probe); the list in
         // global memory is write-only here unless the frontier outgrows the ring.
-        int head = 0, tail = 1;
+        int head = 0, tail = 1, victim = 0;
+        if (lane < FIT_CT) cid[lane] = -1;                                      // the cached answers belong to one component
         if (lane == 0) {
             const int sr = spx / P.w, sc = spx - sr * P.w;
             const unsigned rc0 = ((unsigned)sr << 16) | (unsigned)sc;
@@ -171,7 +176,18 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             head += cnt;
             const int r = (int)(prc >> 16) + ndr, c = (int)(prc & 0xFFFFu) + ndc;
             const size_t po = (size_t)r * P.pitch + c;                          // parents are interior pixels: in range
-            const unsigned own = __ldcg(owner + po);
+            // Is the candidate a pixel of this component that is not listed yet?  The answer lives in the owner plane (one memory
+            // round trip per step: the whole cost of a long walk), so the warp keeps the answer for the last eight 32 x 32 tiles it
+            // touched as bitmaps in shared memory: a step whose candidates all fall into cached tiles costs no global load.
+            const int tid_ = ((r >> 5) << 16) | (c >> 5);
+            int cslot = -1;
+#pragma unroll
+            for (int k = 0; k < FIT_CT; ++k) cslot = (cid[k] == tid_) ? k : cslot;
+            const bool miss = act && cslot < 0;
+            const bool any_miss = __any_sync(0xffffffffu, miss);
+            bool mine;
+            if (!any_miss) mine = act && ((ctile[(act ? cslot : 0) * 32 + (r & 31)] >> (c & 31)) & 1u);
+            else mine = __ldcg(owner + po) == ckey;
             // A pixel can be the neighbour of several of the (up to four) parents of this step; the reference's FIFO order
             // gives it to the first of them, i.e. the lowest lane.  Two candidates coincide exactly when the pixel lies in
             // the 3x3 neighbourhood of an earlier parent, so three shuffles (independent of the memory round trip above)
@@ -183,7 +199,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
                 const int dr_ = r - (int)(o >> 16), dc_ = c - (int)(o & 0xFFFFu);
                 dup |= (q < pslot) && (dr_ >= -1) && (dr_ <= 1) && (dc_ >= -1) && (dc_ <= 1);
             }
-            const bool take = act && (own == ckey) && !dup;
+            const bool take = act && mine && !dup;
             const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
             const unsigned tm = __ballot_sync(0xffffffffu, take);
             __syncwarp();                                                       // every lane has read its parent: ring entries may be overwritten
@@ -192,9 +208,26 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
                 if (pos < n) __stcg(px + pos, rcq);
                 ring[pos & (FIT_RING - 1)] = rcq;
                 __stcg(owner + po, listed);
+                if (cslot >= 0) atomicAnd(&ctile[cslot * 32 + (r & 31)], ~(1u << (c & 31)));
             }
             tail += __popc(tm);
             __syncwarp();
+            if (any_miss) {                                                     // bring in the tile of the first candidate that missed
+                const int leader = __ffs(__ballot_sync(0xffffffffu, miss)) - 1;
+                const int ltid = __shfl_sync(0xffffffffu, tid_, leader);
+                const int y0 = (ltid >> 16) << 5, x0 = (ltid & 0xFFFF) << 5;
+                const int v = victim; victim = (victim + 1) % FIT_CT;
+                const int x = x0 + lane;
+                unsigned oo[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) oo[i] = (y0 + i < P.h && x < P.pitch) ? __ldcg(owner + (size_t)(y0 + i) * P.pitch + x) : 0u;
+                unsigned wordv = 0u;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) { const unsigned bal = __ballot_sync(0xffffffffu, oo[i] == ckey); wordv = (lane == i) ? bal : wordv; }
+                ctile[v * 32 + lane] = wordv;
+                if (lane == 0) cid[v] = ltid;
+                __syncwarp();
+            }
         }
         // tail == n by construction (the committed flood counted the same set)
         const int m = min(tail, n);
