@@ -112,7 +112,7 @@ __device__ __forceinline__ void seq_accumulate(float (*stage)[32], const float (
 }
 
 __global__ void __launch_bounds__(FIT_WARPS * 32)
-k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
+k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int use_cache)
 {
     // per warp: the large-component path uses stage[3][32], val[FIT_RING], ring[FIT_RING]; the sub-warp path the same memory as
     // four sets of stage[3][kFitSmallMax], val[kFitSmallMax], ring[kFitSmallMax]
@@ -183,6 +183,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             int cslot = -1;
 #pragma unroll
             for (int k = 0; k < FIT_CT; ++k) cslot = (cid[k] == tid_) ? k : cslot;
+            if (!use_cache) cslot = -1;                                         // LRB_FIT_NOCACHE=1 (experiments): every step probes the owner plane
             const bool miss = act && cslot < 0;
             const bool any_miss = __any_sync(0xffffffffu, miss);
             bool mine;
@@ -212,7 +213,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl)
             }
             tail += __popc(tm);
             __syncwarp();
-            if (any_miss) {                                                     // bring in the tile of the first candidate that missed
+            if (any_miss && use_cache) {                                        // bring in the tile of the first candidate that missed
                 const int leader = __ffs(__ballot_sync(0xffffffffu, miss)) - 1;
                 const int ltid = __shfl_sync(0xffffffffu, tid_, leader);
                 const int y0 = (ltid >> 16) << 5, x0 = (ltid & 0xFFFF) << 5;
@@ -485,7 +486,8 @@ void launch_fit(const Planes & P, const Seeds & S, const Comps & K, FrameCtrl * 
     once.run([&] { cudaFuncSetAttribute(k_fit_segments, cudaFuncAttributePreferredSharedMemoryCarveout, 50); });
     k_comp_select<<<n_slots, 1024, 0, st>>>(S, K, ctrl, rounds_total);
     dim3 grid(max(1, 148 * 8 / max(1, min(n_slots, 8))), n_slots);
-    k_fit_segments<<<grid, FIT_WARPS * 32, 0, st>>>(P, S, K, ctrl);
+    static const int use_cache = getenv("LRB_FIT_NOCACHE") ? 0 : 1;
+    k_fit_segments<<<grid, FIT_WARPS * 32, 0, st>>>(P, S, K, ctrl, use_cache);
 }
 
 void launch_labels(const Planes & P, const Comps & K, FrameCtrl * ctrl, int * labels, int slot, cudaStream_t st)
