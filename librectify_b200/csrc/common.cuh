@@ -125,9 +125,13 @@ struct Planes {                 // one frame slot = one set of planes; slot s li
     size_t stride;              // elements per slot plane (pitch * h rounded up)
     const float * img;          // input frames (may alias user memory): img + s * img_stride + r * img_pitch + c
     size_t img_stride; int img_pitch;
-    float * dx; float * dy; float * mag;
-    uint8_t * bin; uint8_t * mask8;
-    uint8_t * vis;              // visited mask of the flood (reference filter.cpp `visited`), cleared per frame
+    float2 * dxy;               // (dx, dy) interleaved: the flood and the fit always want both, and a pixel's pair shares one sector
+    float * mag;
+    uint8_t * bin;
+    // low byte: mask8 (bit b = some 3x3 neighbour has bin b; written by K2, which thereby also clears the high byte for the frame);
+    // high byte: the visited mask of the flood (reference filter.cpp `visited`).  One 16-bit plane instead of two byte planes: a
+    // flood window costs one sector per row for both (a TALL sub-warp window: 32 rows x 64-byte bursts less).
+    unsigned short * mv;
     unsigned * owner;
 };
 

@@ -189,9 +189,8 @@ int ensure_workspace(lrb_engine * e, int w, int h)
     auto layout = [&](char * base) {
         char * p = base;
         e->ws_img_raw = carve<float>(p, plane * G); e->ws_img = e->ws_img_raw + org;
-        e->P.dx = carve<float>(p, plane * G) + org; e->P.dy = carve<float>(p, plane * G) + org; e->P.mag = carve<float>(p, plane * G) + org;
-        e->P.bin = carve<uint8_t>(p, plane * G) + org; e->P.mask8 = carve<uint8_t>(p, plane * G) + org;
-        e->P.vis = carve<uint8_t>(p, plane * G) + org;
+        e->P.dxy = carve<float2>(p, plane * G) + org; e->P.mag = carve<float>(p, plane * G) + org;
+        e->P.bin = carve<uint8_t>(p, plane * G) + org; e->P.mv = carve<unsigned short>(p, plane * G) + org;
         e->owner_raw = carve<unsigned>(p, plane * G); e->P.owner = e->owner_raw + org;
         e->S.us_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.us_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
         e->S.b_mag = carve<unsigned>(p, (size_t)cap_seeds * G); e->S.b_idx = carve<unsigned>(p, (size_t)cap_seeds * G);
@@ -381,7 +380,7 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     // ---- ingest (reference src/image.cpp:11-20: dense copy of a strided, possibly bottom-up buffer) ------------------
     stage(LRB_T_INGEST);
     launch_frame_init(e->S, e->ctrl, n, e->st);
-    CK(cudaMemsetAsync(e->P.vis - ((size_t)kMarginY * e->pitch + kMarginX), 0, e->plane * n, e->st));
+    // (the visited mask needs no memset: K2 writes the whole mask / visited plane of the frame, visited = 0)
     CUtensorMap tm_user; const CUtensorMap * tm = &e->tm_img;
     Planes P1 = e->P; int tma_x = kMarginX, tma_y = kMarginY;      // K1's view: where the input image lives
     if (u8.channels) {

@@ -189,7 +189,7 @@ __device__ __forceinline__ float compute_strip(const float * tile, const Planes 
 #pragma unroll
     for (int a = 0; a < 4; ++a) { rx[a][0] = rx[a][1] = 0ull; ry[a][0] = ry[a][1] = 0ull; }
 
-    float * pdx = P.dx + slot * P.stride; float * pdy = P.dy + slot * P.stride; float * pmag = P.mag + slot * P.stride;
+    float2 * pdxy = P.dxy + slot * P.stride; float * pmag = P.mag + slot * P.stride;
     uint8_t * pbin = P.bin + slot * P.stride;
     const float * trow = tile + ty0 * K1_SW + lane * 4;
 
@@ -234,8 +234,8 @@ __device__ __forceinline__ float compute_strip(const float * tile, const Planes 
                 finish_pair<INTERIOR>(fx[0], fy[0], vy && vc0, vy && vc1, odx.x, odx.y, ody.x, ody.y, omag.x, omag.y, b0, b1);
                 finish_pair<INTERIOR>(fx[1], fy[1], vy && vc2, vy && vc3, odx.z, odx.w, ody.z, ody.w, omag.z, omag.w, b2, b3);
                 const size_t o = (size_t)y * P.pitch + xq;
-                *reinterpret_cast<float4 *>(pdx + o) = odx;
-                *reinterpret_cast<float4 *>(pdy + o) = ody;
+                *reinterpret_cast<float4 *>(pdxy + o) = make_float4(odx.x, ody.x, odx.y, ody.y);
+                *reinterpret_cast<float4 *>(pdxy + o + 2) = make_float4(odx.z, ody.z, odx.w, ody.w);
                 *reinterpret_cast<float4 *>(pmag + o) = omag;
                 *reinterpret_cast<unsigned *>(pbin + o) = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
                 tmax = fmaxf(tmax, fmaxf(fmaxf(omag.x, omag.y), fmaxf(omag.z, omag.w)));

@@ -113,14 +113,15 @@ __device__ __forceinline__ unsigned nms_tile(const float * tmag, const uint8_t *
     unsigned colkeep = 0;
 #pragma unroll
     for (int c = 0; c < 4; ++c) { const int x = xq + c; if (x >= 1 && x < P.w - 1) colkeep |= 0xFFu << (8 * c); }
-    uint8_t * pmask = P.mask8 + slot * P.stride;
+    unsigned short * pmv = P.mv + slot * P.stride;
 #pragma unroll
     for (int j = 0; j < K2_RPT; ++j) {
         const int y = y0 + ty0 + j;
         if (y < P.h && xq < P.wq) {
             const unsigned mword = hor[j] | hor[j + 1] | hor[j + 2];
             const bool vy = (y >= 1) && (y < P.h - 1);
-            *reinterpret_cast<unsigned *>(pmask + (size_t)y * P.pitch + xq) = vy ? (mword & colkeep) : 0u;
+            const unsigned mk = vy ? (mword & colkeep) : 0u;                  // four mask bytes -> four 16-bit entries, visited byte 0
+            *reinterpret_cast<uint2 *>(pmv + (size_t)y * P.pitch + xq) = make_uint2(__byte_perm(mk, 0u, 0x4140u), __byte_perm(mk, 0u, 0x4342u));
         }
     }
 
@@ -369,7 +370,8 @@ __global__ void __launch_bounds__(256) k_seed_rank(Planes P, Seeds S, FrameCtrl 
     S.idx[so + rank] = ix;
     S.bin[so + rank] = (uint8_t)b;
     // flood threshold (1 - 0.25f) * G_b(seed)   (reference src/filter.cpp:119-121)
-    S.thr[so + rank] = __fmul_rn(kTraceKeep, orient_energy(P.dx[po], P.dy[po], b));
+    const float2 gseed = P.dxy[po];
+    S.thr[so + rank] = __fmul_rn(kTraceKeep, orient_energy(gseed.x, gseed.y, b));
     S.status[so + rank] = kStatusLive;
     S.fail_epoch[so + rank] = 0u;
     S.size[so + rank] = 0;

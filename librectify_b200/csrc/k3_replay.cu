@@ -498,7 +498,8 @@ k_seed_replay(Planes P, Seeds S, FrameCtrl * ctrl, int depth_override, int fixup
         const int b = P.bin[po];
         sidx[fr] = ix;
         S.bin[so + fr] = (uint8_t)b;
-        S.thr[so + fr] = __fmul_rn(kTraceKeep, orient_energy(P.dx[po], P.dy[po], b));      // reference src/filter.cpp:119-121
+        const float2 gseed = P.dxy[po];
+        S.thr[so + fr] = __fmul_rn(kTraceKeep, orient_energy(gseed.x, gseed.y, b));       // reference src/filter.cpp:119-121
     }
 #ifdef LRB_FLOOD_STATS
     __syncthreads();

@@ -49,7 +49,7 @@ static __device__ __constant__ const int kDc[8] = {-1, 1, 0, 0, -1, 1, -1, 1};
 // instead of once per BFS level, and the region comes out as the same set the sequential flood reaches — the order in
 // which a connected set is discovered does not change the set.
 struct FloodCtx {
-    const uint8_t * mask8; const uint8_t * vis; const float * dx; const float * dy;
+    const unsigned short * mv; const float2 * dxy;      // mask8 | visited << 8; (dx, dy)
     int w, h, pitch, b;
     float thr, sb, cb;
 };
@@ -86,23 +86,29 @@ __device__ __forceinline__ unsigned long long tile_eligible(const FloodCtx X, in
     const bool h0 = x0 >= 0 && x0 + 16 <= X.pitch, h1 = x0 + 16 >= 0 && x0 + 32 <= X.pitch;      // warp-uniform
     const ptrdiff_t rbase = (ptrdiff_t)min(max(y, 0), X.h - 1) * X.pitch;
     const ptrdiff_t o0 = rbase + (h0 ? x0 : 0), o1 = rbase + (h1 ? x0 + 16 : 0);
-    const uint4 m0 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + o0)), v0 = __ldg(reinterpret_cast<const uint4 *>(X.vis + o0));
-    const uint4 m1 = __ldg(reinterpret_cast<const uint4 *>(X.mask8 + o1)), v1 = __ldg(reinterpret_cast<const uint4 *>(X.vis + o1));
+    // 16-bit entries (mask8 | visited << 8): four 16-byte loads per row, split into mask bytes and visited bytes
+    const uint4 w0 = __ldg(reinterpret_cast<const uint4 *>(X.mv + o0)), w1 = __ldg(reinterpret_cast<const uint4 *>(X.mv + o0) + 1);
+    const uint4 w2 = __ldg(reinterpret_cast<const uint4 *>(X.mv + o1)), w3 = __ldg(reinterpret_cast<const uint4 *>(X.mv + o1) + 1);
+#define LRB_LO(q_) __byte_perm((q_).x, (q_).y, 0x6420u), __byte_perm((q_).z, (q_).w, 0x6420u)
+#define LRB_HI(q_) __byte_perm((q_).x, (q_).y, 0x7531u), __byte_perm((q_).z, (q_).w, 0x7531u)
+    const uint4 m0 = make_uint4(LRB_LO(w0), LRB_LO(w1)), m1 = make_uint4(LRB_LO(w2), LRB_LO(w3));
+    const uint4 v0 = make_uint4(LRB_HI(w0), LRB_HI(w1)), v1 = make_uint4(LRB_HI(w2), LRB_HI(w3));
+#undef LRB_LO
+#undef LRB_HI
     // (2) G_b(p) > thr for every pixel of the tile, row by row with lane = column (coalesced).  Rows outside the
     //     interior are dropped by `rowok` of the lane that keeps them, columns outside it by the `cols` mask below.
     unsigned G = 0;
     if (y0 >= 0 && y0 + 32 <= X.h && x0 >= 0 && x0 + 32 <= X.pitch) {       // the tile lies inside the plane (warp-uniform): no clamping
-        const float * pdx = X.dx + ((ptrdiff_t)y0 * X.pitch + x0 + lane);
-        const float * pdy = X.dy + ((ptrdiff_t)y0 * X.pitch + x0 + lane);
+        const float2 * pg = X.dxy + ((ptrdiff_t)y0 * X.pitch + x0 + lane);
         const int pitch = X.pitch;
 #pragma unroll
         for (int rb = 0; rb < 32; rb += RB) {
-            float gx[RB], gy[RB];
+            float2 gg[RB];
 #pragma unroll
-            for (int i = 0; i < RB; ++i) { gx[i] = __ldg(pdx + (rb + i) * pitch); gy[i] = __ldg(pdy + (rb + i) * pitch); }
+            for (int i = 0; i < RB; ++i) gg[i] = __ldg(pg + (rb + i) * pitch);
 #pragma unroll
             for (int i = 0; i < RB; ++i) {
-                const float g = fabsf(__fadd_rn(__fmul_rn(gx[i], X.sb), __fmul_rn(gy[i], X.cb)));
+                const float g = fabsf(__fadd_rn(__fmul_rn(gg[i].x, X.sb), __fmul_rn(gg[i].y, X.cb)));
                 const unsigned bal = __ballot_sync(0xffffffffu, g > X.thr);
                 G = (lane == rb + i) ? bal : G;
             }
@@ -112,7 +118,8 @@ __device__ __forceinline__ unsigned long long tile_eligible(const FloodCtx X, in
 #pragma unroll 1
         for (int i = 0; i < 32; ++i) {
             const ptrdiff_t ro = (ptrdiff_t)min(max(y0 + i, 0), X.h - 1) * X.pitch + xc;
-            const float g = fabsf(__fadd_rn(__fmul_rn(__ldg(X.dx + ro), X.sb), __fmul_rn(__ldg(X.dy + ro), X.cb)));
+            const float2 gq = __ldg(X.dxy + ro);
+            const float g = fabsf(__fadd_rn(__fmul_rn(gq.x, X.sb), __fmul_rn(gq.y, X.cb)));
             const unsigned bal = __ballot_sync(0xffffffffu, g > X.thr);
             G = (lane == i) ? bal : G;
         }
@@ -316,7 +323,7 @@ __device__ __forceinline__ void flood_one(const Planes & P, const Seeds & S, con
     const size_t pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
     FloodCtx X;
-    X.dx = P.dx + pbase; X.dy = P.dy + pbase; X.mask8 = P.mask8 + pbase; X.vis = P.vis + pbase;
+    X.dxy = P.dxy + pbase; X.mv = P.mv + pbase;
     X.w = P.w; X.h = P.h; X.pitch = P.pitch;
 
     const unsigned key = (epoch << 24) | (unsigned)rank;
@@ -455,8 +462,8 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     int * dst = last_pass ? S.esc2 + so : S.esc + so;
     int * dst_n = last_pass ? &C.esc2_n : &C.esc_n;
     int * q = first_pass ? &C.queue[round] : &C.esc_q;
-    const float * pdx = P.dx + pbase; const float * pdy = P.dy + pbase;
-    const uint8_t * pm8 = P.mask8 + pbase; const uint8_t * pvis = P.vis + pbase;
+    const float2 * pdxy = P.dxy + pbase;
+    const unsigned short * pmv = P.mv + pbase;
     unsigned * owner = P.owner + pbase;
     unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
     const int W = P.w, H = P.h, pitch = P.pitch;
@@ -497,15 +504,17 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
             const int row = !work ? 0 : (wide ? y0 + sub : y0 + sub + G * (k / RUNS_PER_ROW));
             const int col = !work ? 0 : (wide ? x0 + 8 * k : x0 + 8 * (k % RUNS_PER_ROW));
             const ptrdiff_t o = (ptrdiff_t)row * pitch + col;     // idle groups read the first pixels of the plane
-            const float4 a0 = __ldg(reinterpret_cast<const float4 *>(pdx + o)), a1 = __ldg(reinterpret_cast<const float4 *>(pdx + o) + 1);
-            const float4 b0 = __ldg(reinterpret_cast<const float4 *>(pdy + o)), b1 = __ldg(reinterpret_cast<const float4 *>(pdy + o) + 1);
-            uint2 m, v;                                           // 4-byte aligned (x0 is a multiple of 4), not 8
-            m.x = __ldg(reinterpret_cast<const unsigned *>(pm8 + o)); m.y = __ldg(reinterpret_cast<const unsigned *>(pm8 + o) + 1);
-            v.x = __ldg(reinterpret_cast<const unsigned *>(pvis + o)); v.y = __ldg(reinterpret_cast<const unsigned *>(pvis + o) + 1);
+            // eight pixels: 64 contiguous bytes of (dx, dy) pairs, 16 contiguous bytes of mask | visited entries (8-byte aligned: x0 is a multiple of 4)
+            const float4 * qg = reinterpret_cast<const float4 *>(pdxy + o);
+            const float4 a0 = __ldg(qg), a1 = __ldg(qg + 1), a2 = __ldg(qg + 2), a3 = __ldg(qg + 3);
+            const uint2 e0 = __ldg(reinterpret_cast<const uint2 *>(pmv + o)), e1 = __ldg(reinterpret_cast<const uint2 *>(pmv + o) + 1);
+            uint2 m, v;
+            m.x = __byte_perm(e0.x, e0.y, 0x6420u); m.y = __byte_perm(e1.x, e1.y, 0x6420u);
+            v.x = __byte_perm(e0.x, e0.y, 0x7531u); v.y = __byte_perm(e1.x, e1.y, 0x7531u);
             unsigned g = 0u;
 #define LRB_G(val_x, val_y, bit) g |= (fabsf(__fadd_rn(__fmul_rn(val_x, sb), __fmul_rn(val_y, cb))) > sthr) ? (1u << (bit)) : 0u;
-            LRB_G(a0.x, b0.x, 0) LRB_G(a0.y, b0.y, 1) LRB_G(a0.z, b0.z, 2) LRB_G(a0.w, b0.w, 3)
-            LRB_G(a1.x, b1.x, 4) LRB_G(a1.y, b1.y, 5) LRB_G(a1.z, b1.z, 6) LRB_G(a1.w, b1.w, 7)
+            LRB_G(a0.x, a0.y, 0) LRB_G(a0.z, a0.w, 1) LRB_G(a1.x, a1.y, 2) LRB_G(a1.z, a1.w, 3)
+            LRB_G(a2.x, a2.y, 4) LRB_G(a2.z, a2.w, 5) LRB_G(a3.x, a3.y, 6) LRB_G(a3.z, a3.w, 7)
 #undef LRB_G
             const unsigned mb = bits4(m.x, sbin) | (bits4(m.y, sbin) << 4);
             const unsigned vb = bits4(v.x, 0) | (bits4(v.y, 0) << 4);
@@ -619,12 +628,12 @@ k_flood_prune(Planes P, Seeds S, FrameCtrl * ctrl, int round, int slot0)
     if (C.live[round] == 0 || C.flood_overflow) return;
     const int lo = C.win_lo, hi = C.win_hi;
     const size_t so = (size_t)slot * S.cap;
-    const uint8_t * vis = P.vis + (size_t)slot * P.stride;
+    const unsigned short * mv = P.mv + (size_t)slot * P.stride;
     for (int rank = lo + blockIdx.x * blockDim.x + threadIdx.x; rank < hi; rank += gridDim.x * blockDim.x) {
         if (S.status[so + rank] != kStatusLive) continue;
         const unsigned spx = S.idx[so + rank];
         const int sr = spx / P.w, sc = spx - sr * P.w;
-        if (vis[(size_t)sr * P.pitch + sc]) S.status[so + rank] = kStatusDropped;
+        if (mv[(size_t)sr * P.pitch + sc] >> 8) S.status[so + rank] = kStatusDropped;
     }
 }
 
@@ -641,7 +650,7 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
     const unsigned epoch = epoch_first - (unsigned)round;
     const size_t so = (size_t)slot * S.cap, pbase = (size_t)slot * P.stride;
     const unsigned * owner = P.owner + pbase;
-    uint8_t * vis = P.vis + pbase;
+    uint8_t * vis = reinterpret_cast<uint8_t *>(P.mv + pbase) + 1;      // the visited byte of pixel p is vis[2 * p]
     const unsigned * pool = K.pool + (size_t)slot * K.cap_pool;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     // eight lanes per seed, four seeds per warp (the typical region has 6 pixels: profiles/r2_flood_regions.md); four list entries
@@ -675,7 +684,7 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
                 // pass 2: the region is final — it becomes part of the visited mask (whether or not it is kept later)
                 for (int i = sub; i < size; i += 8) {
                     const unsigned w = __ldcg(list + i);
-                    vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
+                    vis[2 * ((size_t)(w >> 16) * P.pitch + (w & 0xFFFFu))] = 1;
                 }
                 if (sub == 0) S.status[so + rank] = key;
             }
@@ -698,7 +707,7 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
             if (!__all_sync(0xffffffffu, m2)) { if (lane == src) { ++live; first = min(first, brank); } continue; }
             for (int i = lane; i < bsize; i += 32) {
                 const unsigned w = __ldcg(bl + i);
-                vis[(size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)] = 1;
+                vis[2 * ((size_t)(w >> 16) * P.pitch + (w & 0xFFFFu))] = 1;
             }
             if (lane == src) S.status[so + brank] = bkey;
         }
@@ -743,8 +752,8 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_seri
     unsigned * status = S.status + so;
     const size_t pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
-    uint8_t * vis = P.vis + pbase;
-    const float * dx = P.dx + pbase; const float * dy = P.dy + pbase; const uint8_t * mask8 = P.mask8 + pbase;
+    uint8_t * vis = reinterpret_cast<uint8_t *>(P.mv + pbase) + 1;      // the visited byte of pixel p is vis[2 * p], its mask byte vis[2 * p - 1]
+    const float2 * dxy = P.dxy + pbase; const uint8_t * mask8 = reinterpret_cast<const uint8_t *>(P.mv + pbase);
     unsigned * q = K.px + (size_t)slot * K.cap_px;             // not in use yet at this stage
 
     for (int rank = 0; rank < n; ++rank) {
@@ -752,7 +761,7 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_seri
         const unsigned key = (epoch_serial << 24) | (unsigned)rank;
         const unsigned spx = S.idx[so + rank];
         const int sr = spx / P.w, sc = spx - sr * P.w;
-        if (__ldcg(vis + (size_t)sr * P.pitch + sc)) {
+        if (__ldcg(vis + 2 * ((size_t)sr * P.pitch + sc))) {
             if (lane == 0) status[rank] = kStatusDropped;
             __syncwarp();
             continue;
@@ -776,12 +785,13 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_seri
             }
             bool elig = act && r >= 1 && r < P.h - 1 && c >= 1 && c < P.w - 1;
             const size_t po = (size_t)(elig ? r : 0) * P.pitch + (elig ? c : 0);
-            if (elig && !first) elig = (__ldg(mask8 + po) >> b) & 1;
+            if (elig && !first) elig = (__ldg(mask8 + 2 * po) >> b) & 1;
             if (elig && !first) {
-                const float g = fabsf(__fadd_rn(__fmul_rn(__ldg(dx + po), sb), __fmul_rn(__ldg(dy + po), cb)));
+                const float2 gq = __ldg(dxy + po);
+                const float g = fabsf(__fadd_rn(__fmul_rn(gq.x, sb), __fmul_rn(gq.y, cb)));
                 elig = g > thr;
             }
-            if (elig) elig = (__ldcg(vis + po) == 0) && (__ldcg(owner + po) != key);
+            if (elig) elig = (__ldcg(vis + 2 * po) == 0) && (__ldcg(owner + po) != key);
             const unsigned rcq = ((unsigned)r << 16) | (unsigned)(c & 0xFFFF);
             const unsigned long long mkey = elig ? (unsigned long long)rcq : ((1ull << 40) | (unsigned)lane);
             const unsigned same = __match_any_sync(0xffffffffu, mkey);
@@ -795,7 +805,7 @@ k_flood_serial(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, unsigned epoch_seri
         }
         for (int i = lane; i < tail; i += 32) {                 // the region is final: visited
             const unsigned w = __ldcg(q + i);
-            __stcg(vis + (size_t)(w >> 16) * P.pitch + (w & 0xFFFFu), (uint8_t)1);
+            __stcg(vis + 2 * ((size_t)(w >> 16) * P.pitch + (w & 0xFFFFu)), (uint8_t)1);
         }
         if (lane == 0) { S.size[so + rank] = tail; __stcg(status + rank, key); }
         __syncwarp();

@@ -134,7 +134,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int use_cache)
     unsigned * ctile = ctile_all[warp]; int * cid = cid_all[warp];
     const size_t so = (size_t)slot * S.cap, ko = (size_t)slot * K.cap, pbase = (size_t)slot * P.stride;
     unsigned * owner = P.owner + pbase;
-    const float * dx = P.dx + pbase; const float * dy = P.dy + pbase;
+    const float2 * dxy = P.dxy + pbase;
 
     // ---- large components (more than kFitSmallMax pixels): one warp each, handed out dynamically from the list k_comp_select
     // made; the next one is requested before the current one is walked.  Every warp starts here, so the long walks start first.
@@ -245,7 +245,7 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int use_cache)
             if (i < m) {
                 const unsigned rc = LRB_PX(i);
                 const size_t po = (size_t)(rc >> 16) * P.pitch + (rc & 0xFFFFu);
-                t[0] = orient_energy(__ldg(dx + po), __ldg(dy + po), b);
+                { const float2 g = __ldg(dxy + po); t[0] = orient_energy(g.x, g.y, b); }
                 val[i] = t[0];
                 if (small) vring[i] = t[0];
             }
@@ -395,7 +395,8 @@ k_fit_segments(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int use_cache)
             for (int i = sub; i < m; i += 8) {
                 const unsigned rc = sring[i];
                 const size_t po = (size_t)(rc >> 16) * P.pitch + (rc & 0xFFFFu);
-                const float v = orient_energy(__ldg(dx + po), __ldg(dy + po), b);
+                const float2 g = __ldg(dxy + po);
+                const float v = orient_energy(g.x, g.y, b);
                 sval[i] = v; sstage[i] = v;
             }
             __syncwarp();

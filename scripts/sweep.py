@@ -12,6 +12,8 @@ from librectify_b200 import api  # noqa: E402
 from librectify_b200.runner import Runner  # noqa: E402
 from librectify_b200.synth import manhattan_frame  # noqa: E402
 
+if os.environ.get("LRB_LIB_PATH"):           # A/B runs inside one gpurun call: another build of the library
+    api.LIB_PATH = os.environ["LRB_LIB_PATH"]
 W, H, ML = 1920, 1080, 19.2
 shapes = [tuple(int(x) for x in a.split(":")) for a in sys.argv[1:]] or [(4, 8, 64)]
 fmax = max(f for _, _, f in shapes)
