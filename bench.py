@@ -42,8 +42,8 @@ K1_NCU_DRAM_BYTES_PER_PX = (265.444e6 + 802.417e6) / (32 * 1920 * 1080)
 K2_NCU_DRAM_BYTES_PER_PX = (332.646e6 + 61.236e6) / (32 * 1920 * 1080)
 # warp instructions the flood kernels (prune + sub-warp + full-tile + verify, all rounds) issue per 1080p frame: smsp__inst_executed.sum
 # over every flood launch of one 32-frame group, from the tracked launch list named in FLOOD_INSTR_SOURCE
-FLOOD_WARP_INSTR_PER_FRAME = 44.2e6
-FLOOD_INSTR_SOURCE = "profiles/r2c_launches_32frames.md (ncu smsp__inst_executed.sum, 1414 M per 32-frame group: full-tile 845.5 + sub-warp 422.7 + verify 133.8 + prune 12.0)"
+FLOOD_WARP_INSTR_PER_FRAME = 42.6e6
+FLOOD_INSTR_SOURCE = "profiles/r2d_launches_32frames.md (ncu smsp__inst_executed.sum, 1364 M per 32-frame group: full-tile 776.3 + sub-warp 439.9 + verify 136.2 + prune 12.0)"
 
 
 def measured_peaks():
