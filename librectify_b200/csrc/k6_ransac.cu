@@ -190,6 +190,98 @@ __global__ void __launch_bounds__(SC_THREADS) k_score(Lines L, FrameCtrl * ctrl,
     }
 }
 
+// ---- K8, latency form (one or two frames per launch) ----------------------------------------------------------------------
+// A CTA scores 32 hypotheses (lane = hypothesis) with SCW_WARPS warps.  Only the BOOLEAN "inlier" enters a score, and it is
+// order-free; the sum of the inliers' lengths is a float sum in observation order (estimator.h:52-60) and is not.  So the warps
+// share a staged chunk of observations: each tests its slice for the 32 hypotheses and leaves one bit per (hypothesis,
+// observation) in shared memory, and warp 0 then walks the bits of its hypothesis in observation order and adds the lengths —
+// the same sequential sum, with SCW_WARPS times the parallelism on the part that costs (one warp per 32 hypotheses meant 313
+// warps on the whole GPU for a frame: 7.4 ms for the 35 000 observations of a 4K clutter frame, 0.2 ms of a 1080p frame's latency).
+constexpr int SCW_WARPS = 8;
+constexpr int SCW_THREADS = 32 * SCW_WARPS;
+constexpr int SCW_SEG = SC_CHUNK / SCW_WARPS;            // observations of a chunk tested by one warp
+static_assert(SCW_SEG % 32 == 0, "a warp's slice is whole mask words");
+
+__global__ void __launch_bounds__(SCW_THREADS) k_score_wide(Lines L, FrameCtrl * ctrl, int solve, int T)
+{
+    __shared__ float4 s_ad[SC_CHUNK];      // anchor.x, anchor.y, dir.x, dir.y
+    __shared__ float s_len[SC_CHUNK];
+    __shared__ unsigned s_mask[SC_CHUNK / 32][32];     // [word of the chunk][hypothesis]: inlier bits
+    const int slot = blockIdx.y;
+    FrameCtrl & C = ctrl[slot];
+    if (C.n_solves != solve || C.num_obs < 2) return;
+    const int n = C.n_obs[solve];
+    const size_t lo = (size_t)slot * L.cap;
+    const int * obs = L.obs + lo;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + lane;                          // draw index (the same 32 hypotheses in every warp)
+
+    bool ok = false; Hyp h = make_hyp(0.f, 0.f, 0.f);
+    if (i < T) {
+        const int * pr = L.pairs + (size_t)slot * 2 * T + 2 * i;
+        const int a = obs[pr[0]], b = obs[pr[1]];
+        const float * A = L.h + (lo + a) * 3; const float * B = L.h + (lo + b) * 3;
+        const float ex = __fsub_rn(A[0], B[0]), ey = __fsub_rn(A[1], B[1]), ez = __fsub_rn(A[2], B[2]);
+        ok = __fsqrt_rn(sum3(__fmul_rn(ex, ex), __fmul_rn(ey, ey), __fmul_rn(ez, ez))) > kDegeneracyTol;   // line_pencil.cpp:89-98
+        float p0, p1, p2; cross3(A, B, p0, p1, p2);                                                     // line_pencil.cpp:101-108
+        h = make_hyp(p0, p1, p2);
+    }
+    float score = 0.f;
+    for (int c0 = 0; c0 < n; c0 += SC_CHUNK) {
+        const int cn = min(SC_CHUNK, n - c0);
+        __syncthreads();
+        for (int k = threadIdx.x; k < cn; k += SCW_THREADS) {
+            const int q = obs[c0 + k];
+            const float2 an = *reinterpret_cast<const float2 *>(L.anchor + (lo + q) * 2);
+            const float2 di = *reinterpret_cast<const float2 *>(L.dir + (lo + q) * 2);
+            s_ad[k] = make_float4(an.x, an.y, di.x, di.y);
+            s_len[k] = L.len[lo + q];
+        }
+        __syncthreads();
+        // this warp's slice of the chunk: one mask word per 32 observations
+#pragma unroll 1
+        for (int w = 0; w < SCW_SEG / 32; ++w) {
+            const int k0 = warp * SCW_SEG + w * 32;
+            unsigned m = 0u;
+            if (ok && k0 < cn) {
+                const int kn = min(32, cn - k0);
+#pragma unroll 4
+                for (int j = 0; j < kn; ++j) {
+                    const float4 v = s_ad[k0 + j];
+                    // inlier <=> 1 - |v^ . d| < tol (line_pencil.cpp:137-140).  For all but a ~1e-5 sliver of pairs it is decided
+                    // without the IEEE sqrt and the two divisions: (v.d)^2 against |v|^2 (1 - tol -+ delta)^2, delta = 4e-6 — five
+                    // times the worst-case sum of the rounding errors of both evaluations — the sliver takes the
+                    // exact path.
+                    const float vx = h.ideal ? h.px : __fadd_rn(-v.x, h.px), vy = h.ideal ? h.py : __fadd_rn(-v.y, h.py);
+                    const float D = __fadd_rn(__fmul_rn(vx, v.z), __fmul_rn(vy, v.w));
+                    const float Z = __fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy));
+                    const float D2 = __fmul_rn(D, D);
+                    bool in = D2 > __fmul_rn(Z, kInHi);
+                    if (!in && !(D2 < __fmul_rn(Z, kInLo))) in = line_error(h, v.x, v.y, v.z, v.w) < kTolInlier;
+                    m |= in ? (1u << j) : 0u;
+                }
+            }
+            s_mask[warp * (SCW_SEG / 32) + w][lane] = m;
+        }
+        __syncthreads();
+        // the sequential sum, in observation order (adding the +0 of an outlier would change nothing, so outliers are skipped)
+        if (warp == 0 && ok) {
+            const int nw = (cn + 31) / 32;
+            for (int w = 0; w < nw; ++w) {
+                unsigned m = s_mask[w][lane];
+                while (m) { const int j = __ffs(m) - 1; m &= m - 1; score = __fadd_rn(score, s_len[w * 32 + j]); }
+            }
+        }
+    }
+    if (warp != 0) return;
+    if (i < T) L.scores[((size_t)slot * kMaxModels + solve) * T + i] = ok ? score : -1.f;
+    // first strict maximum in draw order (estimator.h:62-70): max score, then lowest draw index
+    unsigned long long key = (ok && score > 0.f) ? (((unsigned long long)__float_as_uint(score) << 32) | (unsigned)(0xFFFFFFFFu - (unsigned)i)) : 0ull;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { const unsigned long long o = __shfl_xor_sync(0xffffffffu, key, s); key = o > key ? o : key; }
+    if (lane == 0 && key) atomicMax(&C.best[solve], key);
+}
+
 // ---- K9: refit on the winner's inliers, assign inliers / garbage, build the next observation list ----------------------
 constexpr int kRefitChunk = 1024;       // terms of the six scatter sums staged per pass
 __global__ void __launch_bounds__(1024) k_refit_assign(Lines L, FrameCtrl * ctrl, int solve, int T)
@@ -326,11 +418,15 @@ void launch_filter_model(const Comps & K, const Lines & L, FrameCtrl * ctrl, int
 void launch_ransac(const Lines & L, FrameCtrl * ctrl, int n_slots, const unsigned * stream, unsigned long long stream_len,
                    int T, cudaStream_t st, cudaEvent_t * ev_score)
 {
+    // 24 KB of shared memory per scoring CTA: state the split (four CTAs per SM) instead of leaving the SM at the driver's maximum (see launch_nms)
+    static PerDeviceOnce once_cv;
+    once_cv.run([&] { cudaFuncSetAttribute(k_score_wide, cudaFuncAttributePreferredSharedMemoryCarveout, 50); });
     for (int k = 0; k < kMaxModels; ++k) {
         launch_sampler(L, ctrl, n_slots, stream, stream_len, k, T, st);
-        dim3 gs((T + SC_THREADS - 1) / SC_THREADS, n_slots);
         if (ev_score) cudaEventRecord(ev_score[2 * k], st);
-        k_score<<<gs, SC_THREADS, 0, st>>>(L, ctrl, k, T);
+        // a large group fills the GPU with one warp per 32 hypotheses; one or two frames need the observations split over warps too
+        if (n_slots <= 2) k_score_wide<<<dim3((T + 31) / 32, n_slots), SCW_THREADS, 0, st>>>(L, ctrl, k, T);
+        else k_score<<<dim3((T + SC_THREADS - 1) / SC_THREADS, n_slots), SC_THREADS, 0, st>>>(L, ctrl, k, T);
         if (ev_score) cudaEventRecord(ev_score[2 * k + 1], st);
         k_refit_assign<<<n_slots, 1024, 0, st>>>(L, ctrl, k, T);
     }
