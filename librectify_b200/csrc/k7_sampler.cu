@@ -188,7 +188,55 @@ __global__ void __launch_bounds__(1024) k_sampler_stitch(Lines L, FrameCtrl * ct
     for (int i = threadIdx.x; i < L.samp_workers; i += blockDim.x)
         t_node[i] = make_int4(L.rec_cnt[w0 + i], L.rec_link[2 * (w0 + i)], L.rec_link[2 * (w0 + i) + 1], (int)L.rec_next[w0 + i]);
     __syncthreads();
-    if (threadIdx.x == 0) {
+    // Fast path: a worker's chain almost always enters the NEXT worker's segment (a segment is ~T / workers samples long and a
+    // sample never spans one), so the chain is 0 -> 1 -> 2 -> ... and the offsets are a prefix sum: one block scan instead of a
+    // serial walk of up to 512 dependent steps (47 us per solve of a single frame's latency).
+    __shared__ int s_end, s_bad, s_wsum[32];
+    if (threadIdx.x == 0) { s_end = L.samp_workers - 1; s_bad = 0; }
+    __syncthreads();
+    const int W = L.samp_workers;
+    const int wi = threadIdx.x;
+    int4 me = make_int4(0, -1, 0, 0);
+    if (wi < W) { me = t_node[wi]; if (me.y < 0) atomicMin(&s_end, wi); }
+    __syncthreads();
+    const int E = s_end;                                             // the chain 0, 1, 2, ... stops here at the latest
+    if (wi < E && me.y != wi + 1) s_bad = 1;
+    __syncthreads();
+    if (!s_bad) {
+        const int bi = (wi > 0 && wi <= E) ? t_node[wi - 1].z : 0;   // where the chain enters this worker's records
+        const int ci = (wi <= E) ? max(me.x - bi, 0) : 0;            // samples it contributes
+        int inc = ci;
+        const int lane = wi & 31, wrp = wi >> 5;
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, sft); if (lane >= sft) inc += v; }
+        if (lane == 31) s_wsum[wrp] = inc;
+        __syncthreads();
+        if (wrp == 0) {
+            int v = s_wsum[lane];
+#pragma unroll
+            for (int sft = 1; sft < 32; sft <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, sft); if (lane >= sft) v += u; }
+            s_wsum[lane] = v;
+        }
+        __syncthreads();
+        inc += wrp ? s_wsum[wrp - 1] : 0;
+        const int off = inc - ci;                                    // samples before this worker's
+        if (wi <= E && off < T) {
+            s_w[wi] = wi; s_b[wi] = bi; s_off[wi] = off;
+            const bool last_seg = (inc >= T) || (wi == E);           // the chain ends inside / with this worker
+            if (last_seg) {
+                const int take = min(ci, T - off);
+                const int total = off + take;
+                unsigned rel;
+                if (total >= T) { const int last = bi + take; rel = (last < me.x) ? L.rec_start[(w0 + wi) * L.samp_records + last] : (unsigned)me.w; }
+                else rel = (unsigned)me.w;
+                s_n = wi + 1; s_total = total;
+                C.samp_done = total;
+                C.stream_pos = C.stream_pos + rel;
+            }
+        }
+    }
+    __syncthreads();
+    if (s_bad && threadIdx.x == 0) {
         int cur = 0, b = 0, off = 0, nseg = 0;
         unsigned long long endpos = C.stream_pos;
         while (cur >= 0 && nseg < L.samp_workers) {
