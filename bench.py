@@ -559,7 +559,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=4096, help="frames of the batch (BASELINE config 3: 4096), sharded over the ranks")
     ap.add_argument("--engines", type=int, default=4, help="engines (streams + workspaces) per GPU")
-    ap.add_argument("--slots", type=int, default=32, help="frame slots per engine (frames per launch group)")
+    ap.add_argument("--slots", type=int, default=64, help="frame slots per engine (frames per launch group)")
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the reference arm (bounded CPU sample)")
     ap.add_argument("--quick", action="store_true", help="skip the extra legs (configs 1/4/5, drop-in, CPU baselines, parity sample)")
     args = ap.parse_args()
