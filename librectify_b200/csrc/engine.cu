@@ -448,7 +448,9 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
     stage(LRB_T_SEEDS);
     launch_seed_order(e->P, Sg, e->ctrl, n, e->S.cap, e->st);
     stage(LRB_T_FLOOD);
-    int rounds = (n <= 2) ? 12 : kInitialRounds;       // one or two frames at the steady window need 9-10 rounds; every blind empty round is four launches of latency
+    // LRB_FORCE_SERIAL (tests): one speculative round, the rest of the seeds by the verbatim serial fallback
+    const bool force_serial = getenv("LRB_FORCE_SERIAL") != nullptr;
+    int rounds = force_serial ? 1 : (n <= 2) ? 12 : kInitialRounds;       // one or two frames at the steady window need 9-10 rounds; every blind empty round is four launches of latency
     e->kernels += launch_flood_rounds(e->P, Sg, e->K, e->ctrl, n, e->S.cap, 0, rounds, epoch_first, e->st);
     e->kernels += 2 + 1 + 3;
     if (debug_sync) {
@@ -493,7 +495,8 @@ int run_group(lrb_engine * e, const float * frames, bool on_device, int n, int w
         }
         if (!more_rounds && !serial && !more_stream) break;
         if (more_rounds && !serial) {
-            if (rounds + 16 <= kMaxRounds) {
+            if (force_serial) serial = true;
+            else if (rounds + 16 <= kMaxRounds) {
                 e->kernels += launch_flood_rounds(e->P, Sg, e->K, e->ctrl, n, e->S.cap, rounds, rounds + 16, epoch_first, e->st);
                 rounds += 16;
             } else serial = true;
