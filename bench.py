@@ -43,6 +43,11 @@ K2_NCU_DRAM_BYTES_PER_PX = (332.646e6 + 61.236e6) / (32 * 1920 * 1080)
 # warp instructions the flood kernels (prune + sub-warp + full-tile + verify, all rounds) issue per 1080p frame: smsp__inst_executed.sum
 # over every flood launch of one 32-frame group, from the tracked launch list named in FLOOD_INSTR_SOURCE
 FLOOD_WARP_INSTR_PER_FRAME = 42.6e6
+# DRAM bytes of the flood kernels per 1080p frame from the same launch list (dram__bytes_read.sum + dram__bytes_write.sum: sub-warp pass
+# 147 MB, full-tile pass 81 MB, verify 22 MB, prune 5 MB) and what a flood would have to read at least: every plane it looks at once
+# (dx, dy 8 B/px, mask | visited 2 B/px) plus one owner stamp written and read per tentative pixel (~0.45 M pixels x 8 B)
+FLOOD_DRAM_BYTES_PER_FRAME = 255e6
+FLOOD_ALGORITHMIC_BYTES_PER_FRAME = 1920 * 1080 * 10 + 0.45e6 * 8
 FLOOD_INSTR_SOURCE = "profiles/r2d_launches_32frames.md (ncu smsp__inst_executed.sum, 1364 M per 32-frame group: full-tile 776.3 + sub-warp 439.9 + verify 136.2 + prune 12.0)"
 
 
@@ -393,6 +398,15 @@ def run_b200(args):
         slots_per_s = 148 * 4 * sm_mhz * 1e6
         flood["achieved"] = FLOOD_WARP_INSTR_PER_FRAME / (alone["flood"] * 1e-3) / slots_per_s
         flood["peak"] = 1.0; flood["frac"] = flood["achieved"]
+        # the same stage seen from the memory side: the sub-warp pass runs at 3.3 TB/s of scattered sectors in a bulk round
+        # (profiles/r2d_ncu_full_flood_bulk_round.md); over the whole stage the floods move ~10x their algorithmic bytes
+        flood["traffic"] = FLOOD_DRAM_BYTES_PER_FRAME
+        flood["hbm_view"] = {"unit": "GB/s", "peak": peak, "dram_bytes_per_frame": FLOOD_DRAM_BYTES_PER_FRAME,
+                             "algorithmic_bytes_per_frame": FLOOD_ALGORITHMIC_BYTES_PER_FRAME,
+                             "dram_GBps_alone": FLOOD_DRAM_BYTES_PER_FRAME / (alone["flood"] * 1e-3) / 1e9,
+                             "frac_of_peak_alone": FLOOD_DRAM_BYTES_PER_FRAME / (alone["flood"] * 1e-3) / 1e9 / peak,
+                             "algorithmic_GBps_alone": FLOOD_ALGORITHMIC_BYTES_PER_FRAME / (alone["flood"] * 1e-3) / 1e9,
+                             "traffic_source": "constant from profiles/r2d_launches_32frames.md, per frame, not measured in this run"}
         flood["note"] = ("issue-slot fraction of the flood stage with ONE engine on the GPU = warp instructions per frame / (148 SMs x 4 schedulers x "
                          "SM clock x stage time per frame); with four engines the stage intervals overlap other engines' kernels, so no in-bench "
                          "fraction is given")

@@ -168,8 +168,8 @@ __global__ void __launch_bounds__(SC_THREADS) k_score(Lines L, FrameCtrl * ctrl,
                 // (v.d)^2 against |v|^2 (1 - tol -+ delta)^2, delta = 4e-6 — five times the worst-case sum of the
                 // rounding errors of both evaluations — the sliver takes the exact path.
                 const float vx = h.ideal ? h.px : __fadd_rn(-v.x, h.px), vy = h.ideal ? h.py : __fadd_rn(-v.y, h.py);
-                const float D = __fadd_rn(__fmul_rn(vx, v.z), __fmul_rn(vy, v.w));
-                const float Z = __fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy));
+                const float D = __fmaf_rn(vx, v.z, __fmul_rn(vy, v.w));       // the fast test may contract: fewer roundings, inside the same delta
+                const float Z = __fmaf_rn(vx, vx, __fmul_rn(vy, vy));
                 const float D2 = __fmul_rn(D, D);
                 bool in = D2 > __fmul_rn(Z, kInHi);
                 if (!in && !(D2 < __fmul_rn(Z, kInLo))) in = line_error(h, v.x, v.y, v.z, v.w) < kTolInlier;
@@ -253,8 +253,8 @@ __global__ void __launch_bounds__(SCW_THREADS) k_score_wide(Lines L, FrameCtrl *
                     // times the worst-case sum of the rounding errors of both evaluations — the sliver takes the
                     // exact path.
                     const float vx = h.ideal ? h.px : __fadd_rn(-v.x, h.px), vy = h.ideal ? h.py : __fadd_rn(-v.y, h.py);
-                    const float D = __fadd_rn(__fmul_rn(vx, v.z), __fmul_rn(vy, v.w));
-                    const float Z = __fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy));
+                    const float D = __fmaf_rn(vx, v.z, __fmul_rn(vy, v.w));       // the fast test may contract: fewer roundings, inside the same delta
+                    const float Z = __fmaf_rn(vx, vx, __fmul_rn(vy, vy));
                     const float D2 = __fmul_rn(D, D);
                     bool in = D2 > __fmul_rn(Z, kInHi);
                     if (!in && !(D2 < __fmul_rn(Z, kInLo))) in = line_error(h, v.x, v.y, v.z, v.w) < kTolInlier;
