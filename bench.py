@@ -330,7 +330,7 @@ def run_b200(args):
         "gpu_launches": int(prof["kernels"]),
         "scoring_pairs_per_frame": float(np.mean(info["n_obs"].sum(axis=1)) * 10000),
         "frames_with_lines": int((info["n_lines"] > 0).sum()), "flood_fallbacks": int(info["flood_fallback"].sum()),
-        "mean_flood_rounds": float(np.mean(info["flood_rounds"])), "mean_seeds": float(np.mean(info["n_seeds"])),
+        "mean_flood_rounds": float(np.mean(info["flood_rounds"])), "max_flood_rounds": int(np.max(info["flood_rounds"])), "mean_seeds": float(np.mean(info["n_seeds"])),
         "device_vs_host_results_identical": same,
         "clocks": clk.summary(),
     }
@@ -390,8 +390,8 @@ def run_b200(args):
             k8["alone"] = {"achieved": a, "frac": a / fp32["ffma"], "frac_of_fma_free_peak": a / fp32["mul_add"]}
         stages["K8_score"] = k8
     sm_mhz = line["clocks"].get("sm_mhz") or 1965.0
-    flood = {"kernel": "k_flood_* (K4: speculative region growing)", "bound": "latency / instruction issue (no HBM or tensor roofline applies: "
-             "data-dependent frontier expansion on L2-resident planes)", "unit": "fraction of issue slots",
+    flood = {"kernel": "k_flood_* (K4: speculative region growing)", "bound": "latency / instruction issue, and scattered-sector DRAM traffic in the sub-warp pass (no single HBM or tensor roofline "
+             "applies: data-dependent frontier expansion; hbm_view gives the memory side)", "unit": "fraction of issue slots",
              "ms_per_frame": st_bench["flood"], "ms_per_frame_alone": alone["flood"] if alone else None,
              "warp_instr_per_frame": FLOOD_WARP_INSTR_PER_FRAME, "instr_source": FLOOD_INSTR_SOURCE}
     if FLOOD_WARP_INSTR_PER_FRAME and alone and alone["flood"] > 0:
