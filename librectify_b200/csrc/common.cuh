@@ -91,6 +91,7 @@ struct FrameCtrl {
     int queue[kMaxRounds + 1]; // queue[r]: next window position handed out in flood round r (warps take seeds dynamically, in priority order)
     int floods_small, floods_mid, floods_esc;   // statistics over all rounds: floods finished in the 8-lane / 16-lane window / handed to the full-tile path
     int esc2_n, esc2_q;        // the same for the second (16-lane) pass -> full-tile path
+    int wl_n;                  // live seeds of the current window as listed by the prune pass (the sub-warp pass floods that list)
     int esc_n, esc_q;          // floods of the current round that outgrew the sub-warp window (escalated to the full-tile path), next one handed out
     int fit_queue;             // next entry of the list of large components handed out by the fit kernel (one warp per component)
     int fit_queue_small;       // next kept component handed out to the sub-warp path (eight lanes per component, four per warp)

@@ -456,7 +456,8 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
     const size_t so = (size_t)slot * S.cap, pbase = (size_t)slot * P.stride;
     // first pass: the window's ranks; second pass: the first pass's escalation list
     const bool first_pass = (G == 8);
-    const int lo = first_pass ? C.win_lo : 0, hi = first_pass ? C.win_hi : C.esc_n;
+    const bool listed = first_pass && (mode & 8);                 // the window's live seeds as listed by the prune pass (S.esc, C.wl_n)
+    const int lo = (first_pass && !listed) ? C.win_lo : 0, hi = first_pass ? (listed ? C.wl_n : C.win_hi) : C.esc_n;
     const int * src = S.esc + so;
     // what this pass cannot finish goes to the next pass's list, from the last sub-warp pass to the full-tile kernel's
     int * dst = last_pass ? S.esc2 + so : S.esc + so;
@@ -476,7 +477,7 @@ k_flood_small(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned 
         if (lane == 0) nxt = atomicAdd(q, NG);                    // the next batch, requested before this one starts
         const int pos = base + grp;
         const bool valid = pos < hi;
-        const int rank = !valid ? 0 : (first_pass ? pos : src[pos]);
+        const int rank = !valid ? 0 : ((first_pass && !listed) ? pos : src[pos]);
         const unsigned st0 = valid ? __ldcg(S.status + so + rank) : kStatusDropped;
         const unsigned spx = valid ? S.idx[so + rank] : 0u;
         const int sbin = valid ? S.bin[so + rank] : 0;
@@ -629,11 +630,25 @@ k_flood_prune(Planes P, Seeds S, FrameCtrl * ctrl, int round, int slot0)
     const int lo = C.win_lo, hi = C.win_hi;
     const size_t so = (size_t)slot * S.cap;
     const unsigned short * mv = P.mv + (size_t)slot * P.stride;
-    for (int rank = lo + blockIdx.x * blockDim.x + threadIdx.x; rank < hi; rank += gridDim.x * blockDim.x) {
-        if (S.status[so + rank] != kStatusLive) continue;
-        const unsigned spx = S.idx[so + rank];
-        const int sr = spx / P.w, sc = spx - sr * P.w;
-        if (mv[(size_t)sr * P.pitch + sc] >> 8) S.status[so + rank] = kStatusDropped;
+    // The survivors are listed (S.esc; any order: tentative floods are independent and their stamps carry the rank), so that the
+    // sub-warp pass floods a dense list: from the second round on half of a window's seeds are committed, dropped here, or were
+    // dropped before, and a batch of four seeds with one live seed costs the same as a full one.
+    int * wl = S.esc + so;
+    const int lane = threadIdx.x & 31;
+    for (int r0 = lo + (blockIdx.x * blockDim.x + threadIdx.x - lane); r0 < hi; r0 += gridDim.x * blockDim.x) {
+        const int rank = r0 + lane;
+        bool keep = rank < hi && S.status[so + rank] == kStatusLive;
+        if (keep) {
+            const unsigned spx = S.idx[so + rank];
+            const int sr = spx / P.w, sc = spx - sr * P.w;
+            if (mv[(size_t)sr * P.pitch + sc] >> 8) { S.status[so + rank] = kStatusDropped; keep = false; }
+        }
+        const unsigned bm = __ballot_sync(0xffffffffu, keep);
+        if (bm == 0u) continue;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&C.wl_n, __popc(bm));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (keep) wl[base + __popc(bm & ((1u << lane) - 1u))] = rank;
     }
 }
 
@@ -733,6 +748,7 @@ k_flood_verify(Planes P, Seeds S, Comps K, FrameCtrl * ctrl, int round, unsigned
         const int nlo = failed ? min(firstf, hi) : hi;
         const int nhi = min(n, hi + max(0, budget - failed));
         C.win_lo = nlo; C.win_hi = nhi;
+        C.wl_n = 0;
         C.win_live = 0; C.win_first = 0x7fffffff; C.win_blocks = 0; C.pool_cursor = 0; C.esc_n = 0; C.esc_q = 0; C.esc2_n = 0; C.esc2_q = 0;
         C.live[round + 1] = failed + (n - hi);                       // seeds that may still have to flood
         C.rounds_run = round + 1;
@@ -857,7 +873,9 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
             // what the 8-lane pass escalates (those floods are long lines, not slightly larger blobs) and costs 7 % of the job
             // throughput (profiles/r2_flood_regions.md), so it is off by default
             static const bool mid = [] { const char * v = getenv("LRB_FLOOD_MID"); return v && atoi(v) != 0; }();
-            k_flood_small<8, 8><<<gs, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode, mid ? 0 : 1);
+            // from the second round on the first pass floods the prune pass's list of survivors (not with the middle pass: it owns S.esc)
+            const int list_mode = (prune && r > 0 && !mid) ? 8 : 0;
+            k_flood_small<8, 8><<<gs, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode | list_mode, mid ? 0 : 1);
             LRB_TRACE_SYNC("sub-warp pass (8 lanes)");
             if (mid) {
                 k_flood_small<16, 6><<<gm, FL_WARPS * 32, 0, st>>>(P, S, K, ctrl, r, epoch_first, s0, small_mode, 1);
