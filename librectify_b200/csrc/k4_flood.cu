@@ -835,9 +835,11 @@ int launch_flood_rounds(const Planes & P, const Seeds & S, const Comps & K, Fram
                          int round_begin, int round_end, unsigned epoch_first, cudaStream_t st)
 {
     // flood: a resident set of CTAs per frame, warps pull seeds from the frame's queue; verify: warps striding over the window
-    // register budget of the flood kernel: MINB resident CTAs per SM (LRB_FLOOD_MINB=4|5|6|8 for experiments; 4 loads a tile's 32 rows in one batch)
+    // register budget of the flood kernel: 4 resident CTAs per SM at 128 registers, a tile's 32 rows loaded in one batch (default), or
+    // LRB_FLOOD_MINB=6: 6 CTAs at 80 registers, two batches of 16 rows.  3, 5, 7 and 8 CTAs were measured too and pruned from the build:
+    // every smaller budget is slower (profiles/r2c_experiments.md)
     static const int minb = [] { const char * v = getenv("LRB_FLOOD_MINB"); return v ? atoi(v) : 4; }();
-    auto kern = (minb >= 8) ? k_flood_round<8, 16> : (minb == 6) ? k_flood_round<6, 16> : (minb == 4) ? k_flood_round<4, 32> : (minb == 7) ? k_flood_round<6, 32> : (minb == 3) ? k_flood_round<5, 32> : k_flood_round<5, 16>;
+    auto kern = (minb == 6) ? k_flood_round<6, 16> : k_flood_round<4, 32>;
     static PerDeviceOnce once; static int per_sm_d[PerDeviceOnce::kMaxDev], n_sm_d[PerDeviceOnce::kMaxDev];
     const int d = once.run([&] {
         const int dv = PerDeviceOnce::dev();
